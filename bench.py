@@ -1,0 +1,389 @@
+#!/usr/bin/env python
+"""Benchmark of the edge-preserving-filter hot path (BASELINE.json).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+Default workload (N = 1): BASELINE.json configs[1] -- adaptive bilateral filter, radius 7 (ksize 15), on a synthetic
+3840x2160 RGB image, one B200.  A "step" is one pass of the filter over one frame.  At N > 1 (torchrun, one process
+per GPU) every rank filters its own frames (frames are independent: no data-path collective, weak scaling) and the
+time is the max over ranks.  Other workloads (--workload): bf_8k_r15 (configs[3]; at N > 1 the image is cut into row
+strips with radius-deep halos, strong scaling), btf_4k (configs[2]), bf_lenna (configs[0] geometry), bf_1080p /
+abf_1080p / btf_1080p (configs[4] frames).
+
+One JSON line on stdout.  `value` = whole-job Mpixel/s with inputs resident in HBM; `e2e` = the same through the
+public API with pinned HOST buffers, H2D + kernel + D2H inside the timed region, two frames in flight; `roofline` =
+the dominant kernel against the measured HBM peak (MEASURED_PEAKS.json) -- the stencil kernels are issue-bound, not
+HBM-bound, so `issue` gives the achieved taps/s and the estimated issue-slot utilisation next to it; `cpu_baseline`
+= the reference's own C++ CPU path (oracle/_ref/libvip_ref_cpu.so, compiled unmodified from the reference) on a
+bounded sample, on this box's host cores.
+
+--impl reference times the reference's CPU implementation of the same workload (bounded sample per step).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+WORKLOADS = {
+    # name: (filter, width, height, ksize, nitr, description)
+    "abf_4k_r7": ("abf", 3840, 2160, 15, 0, "adaptive bilateral filter radius=7 on synthetic 3840x2160 RGB (BASELINE configs[1])"),
+    "btf_4k": ("btf", 3840, 2160, 9, 3, "bilateral texture filter k=9, 3 iterations on synthetic 3840x2160 RGB (configs[2])"),
+    "bf_8k_r15": ("bf", 7680, 4320, 31, 0, "bilateral filter radius=15 on synthetic 7680x4320 RGB, row strips + halos (configs[3])"),
+    "bf_lenna": ("bf", 512, 512, 11, 0, "bilateral filter radius=5 on a 512x512 RGB image (configs[0] geometry)"),
+    "bf_4k_r5": ("bf", 3840, 2160, 11, 0, "bilateral filter radius=5 on synthetic 3840x2160 RGB"),
+    "bf_1080p": ("bf", 1920, 1080, 9, 0, "bilateral filter k=9 on 1080p frames (configs[4])"),
+    "abf_1080p": ("abf", 1920, 1080, 9, 0, "adaptive bilateral filter k=9 on 1080p frames (configs[4])"),
+    "btf_1080p": ("btf", 1920, 1080, 9, 3, "bilateral texture filter k=9 nitr=3 on 1080p frames (configs[4])"),
+}
+L2_BYTES = 126 * 1024 * 1024
+
+# non-zero taps of the circular mask and the per-tap instruction estimates of DESIGN.md
+def mask_taps(r):
+    return sum(1 for y in range(-r, r + 1) for x in range(-r, r + 1) if x * x + y * y <= r * r)
+
+
+def synth_frame(w, h, seed):
+    """S-rand: i.i.d. uniform bytes (content-independent, like the reference's test fixtures)."""
+    return np.random.RandomState(seed).randint(0, 256, size=(h, w, 3), dtype=np.uint8)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def mark(self):
+        return len(self.rows)
+
+    def stop(self, first=0):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = self.rows[first:] or self.rows
+        sm, mx, reasons = [], [], set()
+        for r in rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7), ("sw_power_cap", 8)):
+                if len(r) > col and r[col].lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference(filt, w, h, ksize, nitr, sample_rows, threads, repeats=1):
+    """The reference's own CPU path on a full-width crop of `sample_rows` rows; returns (Mpixel/s, kind, cores, what)."""
+    import _oracle as O
+    img = synth_frame(w, sample_rows, 42)
+    dst = np.empty_like(img)
+    if O.have_ref_cpu():
+        R = O.ref_cpu()
+        kind = "reference"
+        cores = threads or (os.cpu_count() or 1)
+        R.ref_set_num_threads(cores)
+        if filt == "bf":
+            run = lambda: R.ref_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0)
+        elif filt == "abf":
+            run = lambda: R.ref_adaptive_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0)
+        else:
+            run = lambda: R.ref_bilateral_texture_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, nitr)
+    else:
+        kind = "port"
+        L = O.oracle()
+        L.vipo_set_num_threads(threads or 0)
+        cores = L.vipo_get_num_threads()
+        if filt == "bf":
+            run = lambda: L.vipo_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0, 1)
+        elif filt == "abf":
+            run = lambda: L.vipo_adaptive_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0, 1)
+        else:
+            run = lambda: L.vipo_bilateral_texture_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, nitr, 1)
+    best = float("inf")
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        run()
+        best = min(best, time.perf_counter() - t0)
+    mpix = w * sample_rows / best / 1e6
+    what = f"{w}x{sample_rows} full-width crop of the workload frame (seed 42), best of {repeats}, {best * 1e3:.1f} ms"
+    return mpix, kind, cores, what, best
+
+
+def sample_rows_for(filt, w, h, ksize):
+    taps = ksize * ksize * (2 if filt == "abf" else 1) * (4 if filt == "btf" else 1)
+    # ~1e9 tap evaluations per sample: about a second on a many-core host, bounded on a small one
+    rows = int(1e9 / (taps * w))
+    return max(4 * ksize, min(h, rows - rows % 8))
+
+
+def run_reference_arm(args, wl):
+    filt, w, h, ksize, nitr, desc = wl
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    rows = sample_rows_for(filt, w, h, ksize)
+    # calibrate once so that warmup + steps stay within ~2 minutes whatever the host is
+    _, _, _, _, t_cal = cpu_reference(filt, w, h, ksize, nitr, rows, args.cpu_threads)
+    budget_s = 120.0 / max(1, args.warmup + args.steps)
+    if t_cal > budget_s:
+        rows = max(4 * ksize, int(rows * budget_s / t_cal) // 4 * 4)
+    times = []
+    cores = kind = what = None
+    for i in range(args.warmup + args.steps):
+        mp, kind, cores, what, t = cpu_reference(filt, w, h, ksize, nitr, rows, args.cpu_threads)
+        if i >= args.warmup:
+            times.append(t)
+    ms = 1e3 * float(np.mean(times))
+    value = w * rows / (ms * 1e-3) / 1e6
+    out = {
+        "impl": "reference", "metric": f"{filt}_throughput", "value": value, "unit": "Mpixel/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "description": desc, "width": w, "height": h, "ksize": ksize, "nitr": nitr,
+                   "sample": f"each step filters a {w}x{rows} full-width crop (bounded sample of the workload frame)"},
+        "cpu_baseline": {"value": value, "unit": "Mpixel/s", "cores": cores, "kind": kind, "sample": what},
+        "e2e": {"value": value, "unit": "Mpixel/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="abf_4k_r7", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-threads", type=int, default=0, help="threads of the CPU baseline (0 = all host cores)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--content", default="rand", choices=["rand", "smooth"], help="synthetic content")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference_arm(args, wl)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import various_image_processings_b200 as vip
+
+    filt, w, h, ksize, nitr, desc = wl
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    radius = ksize // 2
+
+    # ---- work decomposition
+    strong = (filt == "bf" and args.workload == "bf_8k_r15" and world > 1)
+    if strong:
+        y0, y1 = h * rank // world, h * (rank + 1) // world
+        s0, s1 = max(0, y0 - radius), min(h, y1 + radius)
+        strip = vip.Strip(s0, s1 - s0, y0, y0, y1 - y0)
+    else:
+        y0, y1, s0, s1 = 0, h, 0, h
+        strip = None
+    out_rows = y1 - y0
+    frame_bytes = w * h * 3
+    # inputs resident in HBM; rotate over enough distinct frames that in+out exceed the L2
+    n_pool = max(2, int(np.ceil(1.2 * L2_BYTES / (2.0 * w * (s1 - s0) * 3))))
+    n_pool = min(n_pool, 16)
+    if args.content == "rand":
+        frames = [synth_frame(w, h, 42 + 1000 * rank + i) for i in range(n_pool)]
+    else:
+        import _oracle as O
+        frames = [O.smooth_image(w, h, seed=42 + 1000 * rank + i) for i in range(n_pool)]
+    d_src = [torch.from_numpy(np.ascontiguousarray(f[s0:s1])).cuda() for f in frames]
+    d_dst = [torch.empty((out_rows, w, 3), dtype=torch.uint8, device="cuda") for _ in range(n_pool)]
+
+    if filt == "bf":
+        F = vip.CudaBilateralFilter(w, h, ksize)
+        if strong:
+            step = lambda i: F.bilateral_filter_strip(d_src[i % n_pool], d_dst[i % n_pool], strip)
+        else:
+            step = lambda i: F.bilateral_filter_async(d_src[i % n_pool], d_dst[i % n_pool])
+    elif filt == "abf":
+        F = vip.CudaAdaptiveBilateralFilter(w, h, ksize)
+        step = lambda i: F.execute_async(d_src[i % n_pool], d_dst[i % n_pool])
+    else:
+        F = vip.CudaBilateralTextureFilter(w, h, ksize, nitr)
+        step = lambda i: F.execute_async(d_src[i % n_pool], d_dst[i % n_pool])
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    mark = sampler.mark()
+    n0 = vip.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(args.steps):
+        step(i)
+    ev1.record()
+    barrier()
+    launches = vip.launch_count() - n0
+    ms_total = ev0.elapsed_time(ev1)
+    clocks = sampler.stop(mark)
+    if world > 1:
+        t = torch.tensor([ms_total], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_step = ms_total / args.steps
+    pixels_step = (w * h) if strong else (w * h * world)   # strong: one image over all ranks; weak: one frame per rank
+    value = pixels_step / (ms_step * 1e-3) / 1e6
+
+    # ---- end to end through the public API with pinned host buffers, two frames in flight
+    e2e_steps = max(4, min(args.steps, 20))
+    slots = []
+    for s in range(2):
+        src_img, dst_img = vip.DeviceImage(w, s1 - s0, 3), vip.DeviceImage(w, out_rows, 3)
+        hin, hout = vip.PinnedBuffer(w * (s1 - s0) * 3), vip.PinnedBuffer(w * out_rows * 3)
+        hin.array[:] = frames[s % n_pool][s0:s1].reshape(-1)
+        slots.append((src_img, dst_img, hin, hout, torch.cuda.Stream()))
+    if filt == "btf":
+        F2 = [F, vip.CudaBilateralTextureFilter(w, h, ksize, nitr)]   # scratch is per object
+
+    def e2e_step(i):
+        src_img, dst_img, hin, hout, st = slots[i & 1]
+        src_img.upload(hin.array, stream=st)
+        if filt == "bf":
+            if strong:
+                F.bilateral_filter_strip(src_img, dst_img, strip, stream=st)
+            else:
+                F.bilateral_filter_async(src_img, dst_img, stream=st)
+        elif filt == "abf":
+            F.execute_async(src_img, dst_img, stream=st)
+        else:
+            F2[i & 1].execute_async(src_img, dst_img, stream=st)
+        dst_img.download(hout.array, stream=st)
+
+    for i in range(2):
+        e2e_step(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        e2e_step(i)
+    for sl in slots:
+        sl[4].synchronize()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = pixels_step * e2e_steps / e2e_s / 1e6
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+    local_pixels = w * out_rows
+    kernels_per_step = launches / max(args.steps, 1)
+    taps = mask_taps(radius if filt != "btf" else ksize - 1)
+    if filt == "btf":
+        alg_bytes = local_pixels * 9.0                    # dominant kernel = joint bilateral: src + guide in, dst out
+        kernel_ms = None                                  # several kernels per step: see profiles/ for the split
+        instr_per_tap = 9.7
+        taps_per_px = taps * nitr
+    else:
+        alg_bytes = local_pixels * 6.0                    # 3 B in + 3 B out per pixel
+        kernel_ms = ms_step
+        instr_per_tap = 17.9 if filt == "abf" else 8.9
+        taps_per_px = taps
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
+    except (OSError, ValueError):
+        pass
+    roof = {"bound": "hbm", "unit": "GB/s", "peak": hbm_peak, "peak_source": peak_src, "traffic": traffic,
+            "kernel": {"bf": "stencil_kernel<BF>", "abf": "stencil_kernel<ABF>", "btf": "stencil_kernel<JBF>"}[filt],
+            "note": "the bilateral stencils are instruction-issue bound (see 'issue'); HBM traffic is 6-9 B/pixel"}
+    if kernel_ms:
+        roof["achieved"] = alg_bytes / (kernel_ms * 1e-3) / 1e9
+        roof["frac"] = roof["achieved"] / hbm_peak
+    else:
+        roof["achieved"] = alg_bytes * nitr / (ms_step * 1e-3) / 1e9
+        roof["frac"] = roof["achieved"] / hbm_peak
+    sm_mhz = clocks.get("sm_mhz") or float(peaks.get("sm_max_mhz", 1965.0))
+    sm_count = torch.cuda.get_device_properties(local_rank).multi_processor_count
+    taps_s = local_pixels * taps_per_px / (ms_step * 1e-3)
+    issue_peak = sm_count * 4 * 32 * sm_mhz * 1e6        # thread-instructions / s at the sampled clock
+    issue = {"taps_per_pixel": taps_per_px, "gtaps_per_s": taps_s / 1e9, "est_instr_per_tap": instr_per_tap,
+             "est_issue_util": taps_s * instr_per_tap / issue_peak, "sm_mhz_used": sm_mhz,
+             "peak_thread_instr_per_s": issue_peak,
+             "note": "estimate = taps/s x SASS instructions per tap (DESIGN.md) / (SMs x 4 x 32 x clock); ncu's smsp__issue_active in profiles/ is the measurement"}
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        rows = sample_rows_for(filt, w, h, ksize)
+        mp, kind, cores, what, _ = cpu_reference(filt, w, h, ksize, nitr, rows, args.cpu_threads, repeats=2)
+        cpu = {"value": mp, "unit": "Mpixel/s", "cores": cores, "kind": kind, "sample": what}
+
+    out = {
+        "metric": f"{filt}_throughput", "value": value, "unit": "Mpixel/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if strong else "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "description": desc, "width": w, "height": h, "ksize": ksize, "nitr": nitr,
+                   "content": args.content, "parallelism": ("row strips + halos" if strong else f"{world} independent frame stream(s)"),
+                   "l2": f"rotating over {n_pool} distinct resident frames ({2 * n_pool * w * (s1 - s0) * 3 >> 20} MiB in+out > 126 MiB L2)",
+                   "e2e": "pinned host buffers, upload + filter + download per step, two frames in flight on two streams"},
+        "e2e": {"value": e2e_value, "unit": "Mpixel/s", "h2d_bytes_per_step": w * (s1 - s0) * 3 * world,
+                "d2h_bytes_per_step": w * out_rows * 3 * world, "steps": e2e_steps},
+        "gpu_launches": int(launches), "kernels_per_step": kernels_per_step,
+        "roofline": roof, "issue": issue, "cpu_baseline": cpu, "clocks": clocks,
+    }
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,220 @@
+/*
+ * vip_c_api.h -- C ABI of the B200-native edge-preserving-filter library (libvip_b200.so).
+ *
+ * This is the drop-in boundary.  The reference (yuyuyu-bot/various_image_processings) has no
+ * FFI layer of its own: its boundary is the set of C++ classes in include/cuda/ (CudaBilateralFilter,
+ * CudaAdaptiveBilateralFilter, CudaBilateralTextureFilter, DeviceImage<T>, cuda_gradient<T>).  Those classes
+ * are re-provided, with the same names and signatures, by include/cuda/ (hpp) in this repository and are
+ * implemented in plain C++ on top of the entry points below; every entry point cites the reference interface
+ * it replaces.  The library is linked against the CUDA runtime only: no torch types, no C++ types, no
+ * exceptions cross this boundary.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a positive cudaError_t value when the CUDA runtime failed, or a
+ *     negative VIP_E_* code for argument errors.  Nothing is printed, nothing throws.  (The reference prints
+ *     cudaGetLastError() to stderr and carries on -- src/host_utilities.hpp:7-13; the C++ wrappers in
+ *     include/cuda keep that behaviour on top of these codes.)
+ *   - images are tightly packed, interleaved 8-bit BGR (3 bytes / pixel, pitch = 3*width), like the
+ *     reference (src/bilateral_filter_impl.cu:20); borders replicate (clamp), (:50-51).
+ *   - `d_` pointers are device pointers on the CURRENT device; `stream` is a cudaStream_t passed as void*
+ *     (NULL = legacy default stream).  All run calls are asynchronous with respect to the host; the C++
+ *     wrappers add the cudaDeviceSynchronize() the reference performs after every public call.
+ *   - in-place operation (d_src == d_dst) is not supported (same as the reference).
+ *   - ksize must be odd and >= 1 (the reference silently misbehaves for even ksize, SURVEY.md 9.4;
+ *     VIP_E_KSIZE is returned instead).
+ *
+ * Row strips (the multi-GPU driver): every filter has a *_strip variant.  The filter object is
+ * created with the FULL image size; a strip call describes which rows the device buffers hold and which rows
+ * are to be produced (struct vip_strip).  Coordinates are clamped against the full image only, so strip
+ * results are bit-identical to the corresponding rows of a whole-image call.
+ */
+#ifndef VIP_C_API_H
+#define VIP_C_API_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VIP_API __attribute__((visibility("default")))
+
+/* ---- status codes ------------------------------------------------------------------------------------ */
+#define VIP_OK 0
+#define VIP_E_NULL (-1)      /* NULL handle / pointer                                   */
+#define VIP_E_SIZE (-2)      /* width/height/channels/rows out of range                 */
+#define VIP_E_KSIZE (-3)     /* ksize even or < 1                                       */
+#define VIP_E_SIGMA (-4)     /* sigma <= 0 or not finite                                */
+#define VIP_E_STRIP (-5)     /* strip rows outside the buffers / missing halo rows      */
+#define VIP_E_ALLOC (-6)     /* host allocation failed                                  */
+#define VIP_E_UNSUPPORTED (-7)
+#define VIP_E_DEVICE (-8)    /* multi-GPU: bad device list / no peer access             */
+
+/* How the spatial / range lookup tables are built:
+ *   VIP_LUT_CUDA : float coefficients + expf   -- src/bilateral_filter_impl.cu:217-238 (default; bit parity
+ *                  with the reference's CUDA classes)
+ *   VIP_LUT_CPU  : double coefficients + exp, rounded to float -- include/cpp/bilateral_filter.hpp:12-37 */
+#define VIP_LUT_CUDA 0
+#define VIP_LUT_CPU 1
+
+/* Which rows a strip call reads and writes.  All row numbers are rows of the FULL image.
+ *   the source (and guide) buffers hold rows [src_y0, src_y0 + src_rows)
+ *   the destination buffer's first row is row dst_y0 of the full image
+ *   rows [out_y0, out_y0 + out_rows) are produced
+ * The source rows must cover [out_y0 - halo, out_y0 + out_rows + halo) intersected with the image, where halo
+ * is vip_*_halo_rows() of the filter. */
+typedef struct vip_strip {
+    int src_y0;
+    int src_rows;
+    int dst_y0;
+    int out_y0;
+    int out_rows;
+} vip_strip;
+
+/* ---- library ------------------------------------------------------------------------------------------ */
+VIP_API const char* vip_version(void);
+/* Human-readable text for a status returned by any function of this header. */
+VIP_API const char* vip_status_string(int status);
+/* Number of kernels this library has launched in the calling process (all threads), for benchmark
+ * accounting ("gpu_launches"). */
+VIP_API unsigned long long vip_launch_count(void);
+
+/* ---- device image container ---------------------------------------------------------------------------
+ * replaces DeviceImage<ElemType> (include/cuda/device_image.hpp:4-16, src/device_image.cu:5-52).
+ * elem_size is 1 (uint8_t) or 4 (float).  upload/download copy exactly width*height*channels elements;
+ * the plain versions block like the reference's thrust::copy, the _async versions enqueue on `stream`
+ * (use pinned host memory for real overlap: vip_host_alloc). */
+typedef struct vip_image vip_image;
+VIP_API int vip_image_create(vip_image** out, int width, int height, int channels, int elem_size);
+VIP_API int vip_image_destroy(vip_image* img);
+VIP_API int vip_image_upload(vip_image* img, const void* host_data);
+VIP_API int vip_image_download(const vip_image* img, void* host_data);
+VIP_API int vip_image_upload_async(vip_image* img, const void* host_data, void* stream);
+VIP_API int vip_image_download_async(const vip_image* img, void* host_data, void* stream);
+VIP_API void* vip_image_data(const vip_image* img);
+VIP_API size_t vip_image_bytes(const vip_image* img);
+/* pinned host memory for the async copies */
+VIP_API int vip_host_alloc(void** out, size_t bytes);
+VIP_API int vip_host_free(void* p);
+VIP_API int vip_stream_synchronize(void* stream);
+VIP_API int vip_device_synchronize(void);
+
+/* ---- bilateral / joint bilateral filter ---------------------------------------------------------------
+ * replaces CudaBilateralFilter (include/cuda/bilateral_filter.hpp:7-29):
+ *   ctor -> CudaBilateralFilter::Impl::Impl, LUT precompute   src/bilateral_filter_impl.cu:204-239
+ *   vip_bf_run  -> Impl::bilateral_filter + kernel            src/bilateral_filter_impl.cu:7-96, 241-258
+ *   vip_jbf_run -> Impl::joint_bilateral_filter + kernel      src/bilateral_filter_impl.cu:98-202, 260-280 */
+typedef struct vip_bf vip_bf;
+VIP_API int vip_bf_create(vip_bf** out, int width, int height, int ksize, float sigma_space, float sigma_color);
+VIP_API int vip_bf_create_ex(vip_bf** out, int width, int height, int ksize, float sigma_space, float sigma_color,
+                             int lut_mode);
+VIP_API int vip_bf_destroy(vip_bf* f);
+VIP_API int vip_bf_run(const vip_bf* f, const uint8_t* d_src, uint8_t* d_dst, void* stream);
+VIP_API int vip_jbf_run(const vip_bf* f, const uint8_t* d_src, const uint8_t* d_guide, uint8_t* d_dst, void* stream);
+VIP_API int vip_bf_run_strip(const vip_bf* f, const uint8_t* d_src, uint8_t* d_dst, const vip_strip* strip,
+                             void* stream);
+VIP_API int vip_jbf_run_strip(const vip_bf* f, const uint8_t* d_src, const uint8_t* d_guide, uint8_t* d_dst,
+                              const vip_strip* strip, void* stream);
+VIP_API int vip_bf_halo_rows(const vip_bf* f); /* = ksize/2 */
+/* Copies of the tables the object holds (for tests): kernel_space is ksize*ksize floats, color_table 768. */
+VIP_API int vip_bf_get_luts(const vip_bf* f, float* kernel_space, float* color_table);
+
+/* ---- adaptive bilateral filter ------------------------------------------------------------------------
+ * replaces CudaAdaptiveBilateralFilter (include/cuda/adaptive_bilateral_filter.hpp:7-24):
+ *   ctor -> Impl::Impl (1536-entry colour table)              src/adaptive_bilateral_filter_impl.cu:117-152
+ *   vip_abf_run -> Impl::execute + kernel                     src/adaptive_bilateral_filter_impl.cu:7-115, 154-171 */
+typedef struct vip_abf vip_abf;
+VIP_API int vip_abf_create(vip_abf** out, int width, int height, int ksize, float sigma_space, float sigma_color);
+VIP_API int vip_abf_create_ex(vip_abf** out, int width, int height, int ksize, float sigma_space, float sigma_color,
+                              int lut_mode);
+VIP_API int vip_abf_destroy(vip_abf* f);
+VIP_API int vip_abf_run(const vip_abf* f, const uint8_t* d_src, uint8_t* d_dst, void* stream);
+VIP_API int vip_abf_run_strip(const vip_abf* f, const uint8_t* d_src, uint8_t* d_dst, const vip_strip* strip,
+                              void* stream);
+VIP_API int vip_abf_halo_rows(const vip_abf* f); /* = ksize/2 */
+
+/* ---- gradient magnitude -------------------------------------------------------------------------------
+ * replaces cuda_gradient<T> / cuda_gradient_impl<T> (include/cuda/gradient.hpp:4-23, src/gradient_impl.cu:7-112).
+ * channels is 1 or 3 in the reference's tests; any channels >= 1 is accepted.  dst is float [height][width].
+ * Like the reference, these return right after the launch. */
+VIP_API int vip_gradient_u8(const uint8_t* d_src, float* d_dst, int width, int height, int channels, void* stream);
+VIP_API int vip_gradient_f32(const float* d_src, float* d_dst, int width, int height, int channels, void* stream);
+VIP_API int vip_gradient_u8_strip(const uint8_t* d_src, float* d_dst, int width, int height, int channels,
+                                  const vip_strip* strip, void* stream);
+
+/* ---- border-replicated integral image -----------------------------------------------------------------
+ * GPU twin of BorderReplicatedIntegralImage<uint8_t,3> (include/cpp/border_replicated_integral_image.hpp:6-85;
+ * the reference has this on the CPU only).  The table is (height+2r+1) x (width+2r+1) x 3 uint32, row 0 and
+ * column 0 zero, cell (Y,X) = sum over the clamp-padded image rows < Y, columns < X.  Arithmetic is modulo
+ * 2^32, so box sums stay exact for any image size.
+ * vip_integral_get_u8c3 evaluates get(x0,y0,x1,y1) (inclusive box sums, :34-47) for n rectangles given as
+ * n x 4 int32 (x0,y0,x1,y1) on the device; out is n x 3 uint32. */
+VIP_API int vip_integral_u8c3(const uint8_t* d_src, uint32_t* d_table, int width, int height, int radius,
+                              void* stream);
+VIP_API int vip_integral_get_u8c3(const uint32_t* d_table, int width, int height, int radius, const int32_t* d_rects,
+                                  int n, uint32_t* d_out, void* stream);
+VIP_API size_t vip_integral_table_elems(int width, int height, int radius);
+/* k x k box mean through the integral image: out[y][x][c] = float(get(x-r,y-r,x+r,y+r)[c]) / (k*k), the
+ * quantity include/cpp/adaptive_bilateral_filter.hpp:53-57 reads from the table. */
+VIP_API int vip_integral_box_mean_u8c3(const uint32_t* d_table, float* d_mean, int width, int height, int radius,
+                                       void* stream);
+
+/* ---- bilateral texture filter -------------------------------------------------------------------------
+ * replaces CudaBilateralTextureFilter (include/cuda/bilateral_texture_filter.hpp:7-17):
+ *   ctor/execute -> Impl::Impl / Impl::execute                src/bilateral_texture_filter_impl.cu:179-214
+ *   vip_btf_blur_rtv -> Impl::compute_blur_and_rtv + kernel   src/bilateral_texture_filter_impl.cu:10-104, 216-237
+ *   vip_btf_guide    -> Impl::compute_guide + kernel          src/bilateral_texture_filter_impl.cu:106-177, 239-256
+ * The joint bilateral step uses (ksize 2k-1, sigma_space k-1, sigma_color sqrt(3)) like the reference (:188).
+ * The object owns its scratch buffers; a run is not re-entrant on the same object (same as the reference). */
+typedef struct vip_btf vip_btf;
+VIP_API int vip_btf_create(vip_btf** out, int width, int height, int ksize, int nitr);
+VIP_API int vip_btf_destroy(vip_btf* f);
+VIP_API int vip_btf_run(vip_btf* f, const uint8_t* d_src, uint8_t* d_dst, void* stream);
+VIP_API int vip_btf_blur_rtv(const vip_btf* f, const uint8_t* d_image, const float* d_magnitude, float* d_blurred,
+                             float* d_rtv, void* stream);
+VIP_API int vip_btf_guide(const vip_btf* f, const float* d_blurred, const float* d_rtv, uint8_t* d_guide,
+                          void* stream);
+/* Rows of halo one iteration needs on each side: (k-1) + k/2 + k/2 + 1. */
+VIP_API int vip_btf_halo_rows_per_iteration(const vip_btf* f);
+/* One iteration on a strip: the buffers hold rows [src_y0, src_y0+src_rows); rows [out_y0, out_y0+out_rows)
+ * of the next iterate are written.  The object must have been created with the FULL image size. */
+VIP_API int vip_btf_iterate_strip(vip_btf* f, const uint8_t* d_src_n, uint8_t* d_dst_n, const vip_strip* strip,
+                                  void* stream);
+VIP_API size_t vip_btf_scratch_bytes(const vip_btf* f);
+
+/* ---- multi-GPU driver (new layer) --------------------------------------------------------
+ * One host process drives n devices of one box.  Large images are cut into contiguous row strips, one per
+ * device, each with a halo of vip_*_halo_rows() rows; halos move by peer-to-peer copies (NVLink) between
+ * neighbouring devices; frames of a batch are dealt round-robin to the devices without communication.
+ * kind: VIP_MG_BF / VIP_MG_ABF / VIP_MG_BTF.  For BF/ABF `nitr` is ignored. */
+#define VIP_MG_BF 0
+#define VIP_MG_ABF 1
+#define VIP_MG_BTF 2
+typedef struct vip_mg vip_mg;
+VIP_API int vip_mg_create(vip_mg** out, const int* device_ids, int n_devices, int kind, int width, int height,
+                          int ksize, float sigma_space, float sigma_color, int nitr);
+VIP_API int vip_mg_destroy(vip_mg* m);
+/* Row range [*y0, *y0 + *rows) owned by device slot `i`. */
+VIP_API int vip_mg_strip_rows(const vip_mg* m, int i, int* y0, int* rows);
+/* Scatter a full host image (pinned or pageable) into the per-device strip buffers (own rows + halos). */
+VIP_API int vip_mg_scatter_host(vip_mg* m, const uint8_t* h_src);
+/* Scatter from a full image resident on device slot 0 using peer copies. */
+VIP_API int vip_mg_scatter_device(vip_mg* m, const uint8_t* d_src_on_dev0);
+/* Run the filter on every strip (all devices concurrently).  For BTF the iterations exchange
+ * halo rows between neighbouring devices with peer copies.  Blocks until all devices are done. */
+VIP_API int vip_mg_run(vip_mg* m);
+/* Same, but returns after enqueueing; vip_mg_wait() blocks. */
+VIP_API int vip_mg_run_async(vip_mg* m);
+VIP_API int vip_mg_wait(vip_mg* m);
+VIP_API int vip_mg_gather_host(vip_mg* m, uint8_t* h_dst);
+/* Device time of the last run, max over devices, from CUDA events (ms). */
+VIP_API int vip_mg_last_run_ms(const vip_mg* m, float* ms);
+/* Independent frames: frame f goes to device slot f % n.  h_src/h_dst hold n_frames packed images (pinned memory
+ * recommended).  Uploads, kernels and downloads of different frames overlap on two streams per device. */
+VIP_API int vip_mg_run_batch_host(vip_mg* m, const uint8_t* h_src, uint8_t* h_dst, int n_frames);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VIP_C_API_H */

@@ -1,0 +1,99 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads, exports every symbol include/vip_c_api.h declares,
+the ctypes table covers the header, and argument validation answers without a GPU (no compute calls here)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+import various_image_processings_b200 as vip
+from various_image_processings_b200 import capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "vip_c_api.h")
+
+
+def declared_symbols():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"VIP_API\s+[\w\s\*]+?\b(vip_\w+)\s*\(", text)))
+
+
+def test_header_symbols_are_exported_and_bound():
+    names = declared_symbols()
+    assert len(names) >= 50
+    L = capi.lib()
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in vip_c_api.h but not exported"
+        assert n in capi.SIGNATURES, f"{n} has no ctypes signature in capi.py"
+    for n in capi.SIGNATURES:
+        assert n in names, f"{n} bound in capi.py but not declared in the header"
+
+
+def test_dynamic_symbol_table_has_no_stray_c_symbols():
+    out = subprocess.check_output(["nm", "-D", "--defined-only", capi.LIB_PATH], text=True)
+    c_syms = [l.split()[-1] for l in out.splitlines() if " T " in l and not l.split()[-1].startswith("_Z")]
+    assert all(s.startswith("vip_") for s in c_syms), c_syms
+
+
+def test_version_and_status_strings():
+    L = capi.lib()
+    assert b"sm_100a" in L.vip_version()
+    assert capi.status_string(0) == "ok"
+    assert "odd" in capi.status_string(-3)
+    assert capi.status_string(2)  # a cudaError_t value maps to the runtime's text
+
+
+def test_argument_validation_precedes_cuda():
+    L = capi.lib()
+    h = C.c_void_p()
+    assert L.vip_bf_create(C.byref(h), 64, 64, 8, 10.0, 30.0) == -3      # even ksize (reference: UB)
+    assert L.vip_bf_create(C.byref(h), 0, 64, 9, 10.0, 30.0) == -2
+    assert L.vip_bf_create(C.byref(h), 64, 64, 9, 0.0, 30.0) == -4
+    assert L.vip_abf_create(C.byref(h), 64, 64, 9, 10.0, float("nan")) == -4
+    assert L.vip_btf_create(C.byref(h), 64, 64, 4, 3) == -3
+    assert L.vip_bf_run(None, None, None, None) == -1
+    assert L.vip_gradient_u8(None, None, 4, 4, 3, None) == -1
+    assert L.vip_integral_table_elems(5, 5, 1) == 8 * 8 * 3
+    assert L.vip_image_create(C.byref(h), 4, 4, 3, 2) == -7
+    assert h.value is None
+
+
+def test_python_mirror_has_reference_interface():
+    # names and defaults of include/cuda/*.hpp
+    import inspect
+    sig = inspect.signature(vip.CudaBilateralFilter.__init__)
+    assert [p for p in sig.parameters][1:6] == ["width", "height", "ksize", "sigma_space", "sigma_color"]
+    assert sig.parameters["ksize"].default == 9 and sig.parameters["sigma_space"].default == 10.0
+    assert sig.parameters["sigma_color"].default == 30.0
+    sig = inspect.signature(vip.CudaBilateralTextureFilter.__init__)
+    assert sig.parameters["ksize"].default == 9 and sig.parameters["nitr"].default == 3
+    for cls, meth in ((vip.CudaBilateralFilter, "bilateral_filter"), (vip.CudaBilateralFilter, "joint_bilateral_filter"),
+                      (vip.CudaAdaptiveBilateralFilter, "execute"), (vip.CudaBilateralTextureFilter, "execute"),
+                      (vip.DeviceImage, "upload"), (vip.DeviceImage, "download"), (vip.DeviceImage, "get")):
+        assert callable(getattr(cls, meth))
+
+
+def test_no_fallback_on_host_tensors():
+    import torch
+    with pytest.raises(ValueError):
+        vip.filters._ptr(torch.zeros(4, dtype=torch.uint8))
+
+
+def test_cpp_dropin_headers_compile_without_cuda(tmp_path):
+    """A user translation unit written against the reference's include paths compiles with plain g++."""
+    src = tmp_path / "user.cpp"
+    src.write_text('#include <cstdint>\n#include "cuda/bilateral_filter.hpp"\n#include "cuda/adaptive_bilateral_filter.hpp"\n'
+                   '#include "cuda/bilateral_texture_filter.hpp"\n#include "cuda/device_image.hpp"\n#include "cuda/gradient.hpp"\n'
+                   "int user(int w, int h, const std::uint8_t* host, std::uint8_t* out) {\n"
+                   "  DeviceImage<std::uint8_t> a(w, h, 3), b(w, h, 3); a.upload(host);\n"
+                   "  CudaBilateralFilter f(w, h, 11); f.bilateral_filter(a.get(), b.get());\n"
+                   "  CudaAdaptiveBilateralFilter g(w, h); g.execute(a.get(), b.get());\n"
+                   "  CudaBilateralTextureFilter t(w, h, 9, 3); t.execute(a.get(), b.get());\n"
+                   "  DeviceImage<float> m(w, h); cuda_gradient(a.get(), m.get(), w, h, 3);\n"
+                   "  b.download(out); return 0; }\n")
+    so = tmp_path / "libuser.so"
+    subprocess.check_call(["g++", "-std=c++17", "-shared", "-fPIC", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(so),
+                           "-L", os.path.dirname(capi.LIB_PATH), "-lvip_b200"])
+    assert so.exists()

@@ -1,0 +1,479 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Everything goes through the C ABI (libvip_b200.so) via
+the Python mirror of the reference's classes.  Bars:
+  * bit-exact vs the oracle in ARITH_CUDA mode (the arithmetic of the reference's CUDA kernels) and vs the
+    reference's own CUDA kernels (oracle/_ref/libvip_ref_cuda.so, built from /root/reference/src unmodified);
+  * max |diff| <= 1 LSB on uint8 outputs vs the reference's CPU implementation (golden vectors) and vs
+    cv2.bilateralFilter -- the tolerance of the reference's own tests (test/bilateral_filter.cu:58-60) and of
+    BASELINE.json's north_star;
+  * integer stages (gradient u8, box sums, integral image, guide) exact.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import _oracle as O
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_vectors.npz"))
+
+
+@pytest.fixture(scope="module")
+def vip():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import various_image_processings_b200 as v
+    torch.cuda.set_device(0)
+    return v
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def run_bf(vip, img, k, ss=10.0, sc=30.0, **kw):
+    h, w, _ = img.shape
+    d = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    vip.CudaBilateralFilter(w, h, k, ss, sc, **kw).bilateral_filter(dev(img), d)
+    return d.cpu().numpy()
+
+
+def run_jbf(vip, img, guide, k, ss=10.0, sc=30.0):
+    h, w, _ = img.shape
+    d = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    vip.CudaBilateralFilter(w, h, k, ss, sc).joint_bilateral_filter(dev(img), dev(guide), d)
+    return d.cpu().numpy()
+
+
+def run_abf(vip, img, k, ss=10.0, sc=30.0, **kw):
+    h, w, _ = img.shape
+    d = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    vip.CudaAdaptiveBilateralFilter(w, h, k, ss, sc, **kw).execute(dev(img), d)
+    return d.cpu().numpy()
+
+
+def run_btf(vip, img, k=9, nitr=3):
+    h, w, _ = img.shape
+    d = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    vip.CudaBilateralTextureFilter(w, h, k, nitr).execute(dev(img), d)
+    return d.cpu().numpy()
+
+
+def maxdiff(a, b):
+    return int(np.abs(a.astype(int) - b.astype(int)).max())
+
+
+# ------------------------------------------------------------------ reference test cases (test/bilateral_filter.cu)
+def test_bf_reference_fixture(vip):
+    src = G["src_mt42"]
+    got = run_bf(vip, src, 9)
+    assert np.array_equal(got, O.o_bf(src, 9))                 # CUDA arithmetic: exact
+    assert maxdiff(got, G["bf_k9"]) <= 1                        # reference CPU implementation
+    assert maxdiff(got, G["cv2_bilateral_k9"]) <= 1             # the reference test's known answer
+    got_cpu_lut = run_bf(vip, src, 9, lut_mode=vip.capi.VIP_LUT_CPU)
+    assert maxdiff(got_cpu_lut, G["bf_k9"]) <= 1
+
+
+def test_jbf_reference_fixture(vip):
+    src, guide = G["src_mt42"], G["guide_seed7"]
+    assert np.array_equal(run_jbf(vip, src, src, 9), run_bf(vip, src, 9))
+    got = run_jbf(vip, src, guide, 9)
+    assert np.array_equal(got, O.o_jbf(src, guide, 9))
+    assert maxdiff(got, G["jbf_k9_guide7"]) <= 1
+
+
+@pytest.mark.parametrize("k,key", [(9, "abf_k9"), (15, "abf_k15")])
+def test_abf_reference_fixture(vip, k, key):
+    src = G["src_mt42"]
+    got = run_abf(vip, src, k)
+    assert np.array_equal(got, O.o_abf(src, k))
+    assert maxdiff(got, G[key]) <= 1
+
+
+# ------------------------------------------------------------------ sizes, radii, sigmas, content
+SIZES = [(1, 1), (5, 7), (50, 50), (64, 32), (65, 33), (131, 70), (257, 19)]
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+@pytest.mark.parametrize("k", [1, 3, 9, 11])
+def test_bf_sizes(vip, w, h, k):
+    img = O.rand_image(w, h, seed=w + 31 * h + k)
+    assert np.array_equal(run_bf(vip, img, k), O.o_bf(img, k))
+
+
+@pytest.mark.parametrize("k", [5, 13, 17, 21, 31])
+@pytest.mark.parametrize("content", ["rand", "smooth"])
+def test_bf_radii(vip, k, content):
+    img = O.rand_image(97, 75, seed=k) if content == "rand" else O.smooth_image(97, 75, seed=k)
+    assert np.array_equal(run_bf(vip, img, k), O.o_bf(img, k))
+
+
+def test_bf_generic_fallback_radius(vip):
+    img = O.smooth_image(60, 45, seed=2)
+    assert np.array_equal(run_bf(vip, img, 35), O.o_bf(img, 35))        # radius 17 > tiled maximum
+    assert np.array_equal(run_abf(vip, img, 33), O.o_abf(img, 33))
+    g = O.rand_image(60, 45, seed=4)
+    assert np.array_equal(run_jbf(vip, img, g, 33), O.o_jbf(img, g, 33))
+
+
+@pytest.mark.parametrize("ss,sc", [(1.5, 5.0), (10.0, 30.0), (3.0, 100.0), (50.0, 400.0), (8.0, 1.7320508)])
+def test_bf_sigmas(vip, ss, sc):
+    # small sigma_color -> zero tail / clamped table; huge sigma_color -> full 768-entry table
+    img = O.rand_image(80, 64, seed=9)
+    for k in (9, 31):
+        assert np.array_equal(run_bf(vip, img, k, ss, sc), O.o_bf(img, k, ss, sc))
+    assert np.array_equal(run_abf(vip, img, 9, ss, sc), O.o_abf(img, 9, ss, sc))
+
+
+def test_bf_extreme_content(vip):
+    h, w = 40, 72
+    for img in (np.zeros((h, w, 3), np.uint8), np.full((h, w, 3), 255, np.uint8)):
+        assert np.array_equal(run_bf(vip, img, 11), img)                 # constant images are fixed points
+        assert np.array_equal(run_abf(vip, img, 15), img)
+    chk = ((np.add.outer(np.arange(h), np.arange(w)) % 2) * 255).astype(np.uint8)
+    img = np.stack([chk, 255 - chk, chk], -1)
+    assert np.array_equal(run_bf(vip, img, 11), O.o_bf(img, 11))
+    assert np.array_equal(run_abf(vip, img, 15), O.o_abf(img, 15))
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+def test_jbf_sizes(vip, w, h):
+    img, g = O.rand_image(w, h, seed=w * h), O.smooth_image(w, h, seed=w + h)
+    assert np.array_equal(run_jbf(vip, img, g, 9), O.o_jbf(img, g, 9))
+    assert np.array_equal(run_jbf(vip, img, g, 17, 8.0, 1.7320508), O.o_jbf(img, g, 17, 8.0, 1.7320508))
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+@pytest.mark.parametrize("k", [1, 3, 9, 15])
+def test_abf_sizes(vip, w, h, k):
+    img = O.rand_image(w, h, seed=3 * w + h + k)
+    assert np.array_equal(run_abf(vip, img, k), O.o_abf(img, k))
+
+
+@pytest.mark.parametrize("k", [5, 17, 23, 31])
+def test_abf_radii(vip, k):
+    img = O.smooth_image(90, 70, seed=k)
+    assert np.array_equal(run_abf(vip, img, k), O.o_abf(img, k))
+
+
+# ------------------------------------------------------------------ gradient (test/gradient.cu)
+@pytest.mark.parametrize("ch", [1, 2, 3])
+@pytest.mark.parametrize("w,h", [(50, 50), (1, 1), (2, 9), (1030, 21), (4100, 3)])
+def test_gradient_u8(vip, ch, w, h):
+    s = O.mt_u8(w * h * ch).reshape(h, w, ch)
+    d = torch.empty((h, w), dtype=torch.float32, device="cuda")
+    vip.cuda_gradient(dev(s), d, w, h, ch)
+    torch.cuda.synchronize()
+    assert np.array_equal(d.cpu().numpy(), O.o_gradient(s if ch > 1 else s[..., 0]))
+    if (w, h) == (50, 50) and ch in (1, 3):
+        assert np.array_equal(d.cpu().numpy(), G[f"grad_u8_c{ch}"])
+
+
+@pytest.mark.parametrize("ch", [1, 3])
+def test_gradient_f32(vip, ch):
+    w = h = 50
+    s = O.mt_f32(w * h * ch).reshape(h, w, ch)
+    d = torch.empty((h, w), dtype=torch.float32, device="cuda")
+    vip.cuda_gradient(dev(s), d, w, h, ch)
+    torch.cuda.synchronize()
+    got = d.cpu().numpy()
+    assert np.array_equal(got, O.o_gradient(s if ch > 1 else s[..., 0], O.ARITH_CUDA))
+    np.testing.assert_allclose(got, G[f"grad_f32_c{ch}"], rtol=4 * 1.2e-7)   # EXPECT_FLOAT_EQ of the reference test
+
+
+# ------------------------------------------------------------------ BTF stages (test/bilateral_texture_filter.cu)
+@pytest.mark.parametrize("w,h,k", [(50, 50, 9), (33, 70, 9), (64, 40, 5), (45, 37, 13)])
+def test_blur_rtv_stage(vip, w, h, k):
+    img = O.mt_u8(w * h * 3).reshape(h, w, 3)
+    mag = O.mt_f32(w * h).reshape(h, w)
+    f = vip.CudaBilateralTextureFilter(w, h, k, 1)
+    bl = torch.empty((h, w, 3), dtype=torch.float32, device="cuda")
+    rt = torch.empty((h, w), dtype=torch.float32, device="cuda")
+    f.compute_blur_and_rtv(dev(img), dev(mag), bl, rt)
+    torch.cuda.synchronize()
+    obl, ort = O.o_blur_rtv(img, mag, k, O.ARITH_CUDA)
+    assert np.array_equal(bl.cpu().numpy(), obl)
+    assert np.array_equal(rt.cpu().numpy(), ort)                      # bit-exact incl. the fp64 divide
+    if (w, h, k) == (50, 50, 9):
+        assert np.array_equal(bl.cpu().numpy(), G["btf_blurred_cpu"])
+        np.testing.assert_allclose(rt.cpu().numpy(), G["btf_rtv_cpu"], rtol=4 * 1.2e-7)
+
+
+@pytest.mark.parametrize("w,h,k", [(50, 50, 9), (33, 70, 9), (64, 40, 5), (45, 37, 13)])
+def test_guide_stage(vip, w, h, k):
+    blurred = O.mt_f32(w * h * 3).reshape(h, w, 3)
+    rtv = O.mt_f32(w * h, 1.0).reshape(h, w)
+    f = vip.CudaBilateralTextureFilter(w, h, k, 1)
+    g = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    f.compute_guide(dev(blurred), dev(rtv), g)
+    torch.cuda.synchronize()
+    got = g.cpu().numpy()
+    assert np.array_equal(got, O.o_guide(blurred, rtv, k, O.ARITH_CUDA))
+    if (w, h, k) == (50, 50, 9):
+        # the CPU reference uses glibc expf and unfused multiply-add: at most 1 level, on few pixels
+        assert maxdiff(got, G["btf_guide_cpu"]) <= 1
+
+
+def test_guide_stage_with_ties(vip):
+    # plateaus of equal rtv values: "first in raster order wins" (strict '>', :152-165)
+    w, h, k = 40, 36, 9
+    rtv = (np.add.outer(np.arange(h) // 5, np.arange(w) // 7) % 3).astype(np.float32) * 0.25
+    blurred = O.mt_f32(w * h * 3).reshape(h, w, 3)
+    f = vip.CudaBilateralTextureFilter(w, h, k, 1)
+    g = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    f.compute_guide(dev(blurred), dev(rtv), g)
+    torch.cuda.synchronize()
+    assert np.array_equal(g.cpu().numpy(), O.o_guide(blurred, rtv, k, O.ARITH_CUDA))
+
+
+@pytest.mark.parametrize("w,h,k,nitr", [(64, 48, 9, 3), (50, 50, 9, 1), (37, 41, 5, 2), (96, 64, 9, 0)])
+def test_btf_end_to_end(vip, w, h, k, nitr):
+    img = O.smooth_image(w, h, seed=5) if (w, h) == (64, 48) else O.rand_image(w, h, seed=w)
+    got = run_btf(vip, img, k, nitr)
+    assert np.array_equal(got, O.o_btf(img, k, nitr, O.ARITH_CUDA))
+    if (w, h, k, nitr) == (64, 48, 9, 3):
+        # vs the reference CPU pipeline (own JBF substituted for ximgproc): the argmin can move on
+        # isolated pixels (float vs double epsilon), so report rather than bound tightly
+        d = np.abs(got.astype(int) - G["btf_k9_n3_smooth_cpu"].astype(int))
+        assert (d > 1).mean() < 0.02, f"{(d > 1).mean():.4f} of samples differ by more than 1 LSB from the CPU reference"
+
+
+# ------------------------------------------------------------------ integral image
+@pytest.mark.parametrize("r", [1, 3, 5])
+def test_integral_all_rectangles_5x5(vip, r):
+    src = G["ii_src_5x5"]
+    ii = vip.CudaIntegralImage(5, 5, r)
+    ii.build(dev(src))
+    rects, sums = G[f"ii_rects_r{r}"], G[f"ii_sums_r{r}"]
+    out = torch.empty((len(rects), 3), dtype=torch.int32, device="cuda")
+    ii.get(dev(rects), len(rects), out)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), sums)
+    assert np.array_equal(ii.download_table().reshape(5 + 2 * r + 1, 5 + 2 * r + 1, 3), O.o_integral(src, r))
+
+
+@pytest.mark.parametrize("w,h,r", [(300, 130, 7), (1000, 70, 4), (64, 64, 0), (513, 257, 15)])
+def test_integral_table_and_box_mean(vip, w, h, r):
+    src = O.rand_image(w, h, seed=w + r)
+    ii = vip.CudaIntegralImage(w, h, r)
+    ii.build(dev(src))
+    torch.cuda.synchronize()
+    table = ii.download_table().reshape(h + 2 * r + 1, w + 2 * r + 1, 3)
+    assert np.array_equal(table, O.o_integral(src, r))
+    mean = torch.empty((h, w, 3), dtype=torch.float32, device="cuda")
+    ii.box_mean(mean)
+    torch.cuda.synchronize()
+    pad = np.pad(src.astype(np.int64), ((r, r), (r, r), (0, 0)), mode="edge")
+    k = 2 * r + 1
+    c = np.cumsum(np.cumsum(np.pad(pad, ((1, 0), (1, 0), (0, 0))), 0), 1)
+    box = c[k:, k:] - c[:-k, k:] - c[k:, :-k] + c[:-k, :-k]
+    want = (box.astype(np.float32) / np.float32(k * k)).astype(np.float32)
+    assert np.array_equal(mean.cpu().numpy(), want)
+
+
+# ------------------------------------------------------------------ row strips == whole image (multi-GPU invariant)
+def strips_of(h, n, halo):
+    out = []
+    for i in range(n):
+        y0, y1 = h * i // n, h * (i + 1) // n
+        s0, s1 = max(0, y0 - halo), min(h, y1 + halo)
+        out.append((y0, y1, s0, s1))
+    return out
+
+
+@pytest.mark.parametrize("kind,k", [("bf", 11), ("bf", 31), ("abf", 15), ("jbf", 17)])
+def test_strips_bit_identical(vip, kind, k):
+    w, h = 150, 131
+    img, guide = O.rand_image(w, h, seed=k), O.smooth_image(w, h, seed=k)
+    full = {"bf": lambda: run_bf(vip, img, k), "abf": lambda: run_abf(vip, img, k),
+            "jbf": lambda: run_jbf(vip, img, guide, k)}[kind]()
+    f = vip.CudaAdaptiveBilateralFilter(w, h, k) if kind == "abf" else vip.CudaBilateralFilter(w, h, k)
+    out = np.zeros_like(img)
+    for (y0, y1, s0, s1) in strips_of(h, 3, k // 2):
+        d_src = dev(img[s0:s1])
+        d_dst = torch.zeros((y1 - y0, w, 3), dtype=torch.uint8, device="cuda")
+        st = vip.Strip(s0, s1 - s0, y0, y0, y1 - y0)
+        if kind == "bf":
+            f.bilateral_filter_strip(d_src, d_dst, st)
+        elif kind == "abf":
+            f.execute_strip(d_src, d_dst, st)
+        else:
+            f.joint_bilateral_filter_strip(d_src, dev(guide[s0:s1]), d_dst, st)
+        torch.cuda.synchronize()
+        out[y0:y1] = d_dst.cpu().numpy()
+    assert np.array_equal(out, full)
+
+
+def test_strip_validation(vip):
+    w, h = 64, 64
+    f = vip.CudaBilateralFilter(w, h, 11)
+    d = torch.zeros((32, w, 3), dtype=torch.uint8, device="cuda")
+    with pytest.raises(vip.VipError):      # halo rows missing: rows 27..31 are not in the source strip
+        f.bilateral_filter_strip(d, d.clone(), vip.Strip(32, 32, 32, 32, 32))
+
+
+@pytest.mark.parametrize("kind,k", [("bf", 11), ("abf", 15), ("btf", 9), ("bf", 31)])
+@pytest.mark.parametrize("n", [1, 2, 3])
+def test_multigpu_driver_virtual_devices(vip, kind, k, n):
+    """The strip planner + halo exchange, with the same GPU listed n times (runnable on 1 GPU)."""
+    w, h = 160, 140
+    img = O.smooth_image(w, h, seed=k + n)
+    mg = vip.MultiGpuFilter([0] * n, kind, w, h, ksize=k, nitr=3)
+    got = mg.execute(img)
+    want = {"bf": lambda: run_bf(vip, img, k), "abf": lambda: run_abf(vip, img, k), "btf": lambda: run_btf(vip, img, k, 3)}[kind]()
+    assert np.array_equal(got, want)
+    assert mg.last_run_ms() > 0
+
+
+def test_multigpu_driver_real_devices(vip):
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    w, h = 320, 64 * n
+    img = O.smooth_image(w, h, seed=1)
+    for kind, k in (("bf", 11), ("btf", 9)):
+        mg = vip.MultiGpuFilter(list(range(n)), kind, w, h, ksize=k, nitr=3)
+        got = mg.execute(img)
+        want = run_bf(vip, img, k) if kind == "bf" else run_btf(vip, img, k, 3)
+        assert np.array_equal(got, want)
+
+
+def test_multigpu_batch(vip):
+    w, h, nf = 96, 80, 5
+    frames = np.stack([O.rand_image(w, h, seed=42 + f) for f in range(nf)])
+    out = np.zeros_like(frames)
+    mg = vip.MultiGpuFilter([0, 0], "abf", w, h, ksize=9)
+    mg.execute_batch(frames, out, nf)
+    for f in range(nf):
+        assert np.array_equal(out[f], O.o_abf(frames[f], 9))
+
+
+# ------------------------------------------------------------------ DeviceImage (include/cuda/device_image.hpp)
+def test_device_image_roundtrip(vip):
+    a = O.rand_image(33, 17, seed=1)
+    img = vip.DeviceImage(33, 17, 3)
+    assert np.array_equal(img.download(), np.zeros_like(a))     # value-initialised like thrust::device_vector
+    img.upload(a)
+    assert np.array_equal(img.download(), a)
+    f = vip.DeviceImage(8, 4, 1, np.float32)
+    x = np.arange(32, dtype=np.float32).reshape(4, 8)
+    f.upload(x)
+    assert np.array_equal(f.download(), x)
+    out = vip.DeviceImage(33, 17, 3)
+    vip.CudaBilateralFilter(33, 17, 9).bilateral_filter(img, out)
+    assert np.array_equal(out.download(), O.o_bf(a, 9))
+
+
+# ------------------------------------------------------------------ the reference's own CUDA kernels, run on this GPU
+needs_ref_cuda = pytest.mark.skipif(not O.have_ref_cuda(), reason="oracle/_ref/libvip_ref_cuda.so not built")
+
+
+@needs_ref_cuda
+@pytest.mark.parametrize("w,h,k", [(50, 50, 9), (131, 70, 11), (200, 90, 31)])
+def test_bit_exact_vs_reference_cuda_bf_abf(vip, w, h, k):
+    R = O.ref_cuda()
+    img, guide = O.rand_image(w, h, seed=k), O.smooth_image(w, h, seed=k)
+    d_src, d_guide = dev(img), dev(guide)
+    d_ref = torch.empty_like(d_src)
+    p = R.refcu_bf_create(w, h, k, 10.0, 30.0)
+    R.refcu_bf_run(p, d_src.data_ptr(), d_ref.data_ptr())
+    assert np.array_equal(run_bf(vip, img, k), d_ref.cpu().numpy())
+    R.refcu_jbf_run(p, d_src.data_ptr(), d_guide.data_ptr(), d_ref.data_ptr())
+    assert np.array_equal(run_jbf(vip, img, guide, k), d_ref.cpu().numpy())
+    R.refcu_bf_destroy(p)
+    p = R.refcu_abf_create(w, h, k, 10.0, 30.0)
+    R.refcu_abf_run(p, d_src.data_ptr(), d_ref.data_ptr())
+    assert np.array_equal(run_abf(vip, img, k), d_ref.cpu().numpy())
+    R.refcu_abf_destroy(p)
+
+
+@needs_ref_cuda
+@pytest.mark.parametrize("w,h,nitr", [(64, 48, 3), (150, 100, 2)])
+def test_bit_exact_vs_reference_cuda_btf(vip, w, h, nitr):
+    R = O.ref_cuda()
+    img = O.smooth_image(w, h, seed=nitr)
+    d_src = dev(img)
+    d_ref = torch.empty_like(d_src)
+    p = R.refcu_btf_create(w, h, 9, nitr)
+    R.refcu_btf_run(p, d_src.data_ptr(), d_ref.data_ptr())
+    assert np.array_equal(run_btf(vip, img, 9, nitr), d_ref.cpu().numpy())
+    # stages on the reference test's fixtures
+    mag = O.mt_f32(w * h).reshape(h, w)
+    bl = torch.empty((h, w, 3), dtype=torch.float32, device="cuda")
+    rt = torch.empty((h, w), dtype=torch.float32, device="cuda")
+    bl2, rt2 = torch.empty_like(bl), torch.empty_like(rt)
+    d_mag = dev(mag)
+    R.refcu_btf_blur_rtv(p, d_src.data_ptr(), d_mag.data_ptr(), bl.data_ptr(), rt.data_ptr(), w, h)
+    f = vip.CudaBilateralTextureFilter(w, h, 9, nitr)
+    f.compute_blur_and_rtv(d_src, d_mag, bl2, rt2)
+    torch.cuda.synchronize()
+    assert torch.equal(bl, bl2) and torch.equal(rt, rt2)
+    blurred = dev(O.mt_f32(w * h * 3).reshape(h, w, 3))
+    rtv = dev(O.mt_f32(w * h, 1.0).reshape(h, w))
+    g1 = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    g2 = torch.empty_like(g1)
+    R.refcu_btf_guide(p, blurred.data_ptr(), rtv.data_ptr(), g1.data_ptr(), w, h)
+    f.compute_guide(blurred, rtv, g2)
+    torch.cuda.synchronize()
+    assert torch.equal(g1, g2)
+    R.refcu_btf_destroy(p)
+
+
+@needs_ref_cuda
+def test_bit_exact_vs_reference_cuda_gradient(vip):
+    R = O.ref_cuda()
+    w, h = 131, 77
+    for ch in (1, 3):
+        s = dev(O.mt_u8(w * h * ch).reshape(h, w, ch))
+        a = torch.empty((h, w), dtype=torch.float32, device="cuda")
+        b = torch.empty_like(a)
+        R.refcu_gradient_u8(s.data_ptr(), a.data_ptr(), w, h, ch)
+        vip.cuda_gradient(s, b, w, h, ch)
+        torch.cuda.synchronize()
+        assert torch.equal(a, b)
+        sf = dev(O.mt_f32(w * h * ch).reshape(h, w, ch))
+        R.refcu_gradient_f32(sf.data_ptr(), a.data_ptr(), w, h, ch)
+        vip.cuda_gradient(sf, b, w, h, ch)
+        torch.cuda.synchronize()
+        assert torch.equal(a, b)
+
+
+# ------------------------------------------------------------------ BASELINE.json sizes: size-independent properties
+def fnv_rows(a):
+    return O.fnv1a64(np.ascontiguousarray(a).tobytes())
+
+
+@pytest.mark.parametrize("kind,w,h,k", [("abf", 3840, 2160, 15), ("bf", 7680, 4320, 31), ("bf", 512, 512, 11)])
+def test_full_size_spot_rows_and_strips(vip, kind, w, h, k):
+    rs = np.random.RandomState(42)
+    img = rs.randint(0, 256, size=(h, w, 3)).astype(np.uint8)
+    got = run_abf(vip, img, k) if kind == "abf" else run_bf(vip, img, k)
+    # spot rows against the oracle (first, last, a middle band crossing a tile boundary)
+    for y0, rows in ((0, 2), (h - 2, 2), (h // 2 - 1, 2)) if w > 4000 else ((0, 3), (h - 3, 3), (1055 % h, 3), (31, 2)):
+        want = O.o_rows(kind, img, y0, rows, k)
+        assert np.array_equal(got[y0:y0 + rows], want), f"rows {y0}..{y0 + rows}"
+    # strips (8 ranks) reproduce the whole-image result bit for bit
+    f = vip.CudaAdaptiveBilateralFilter(w, h, k) if kind == "abf" else vip.CudaBilateralFilter(w, h, k)
+    for (y0, y1, s0, s1) in strips_of(h, 8, k // 2)[2:4]:
+        d_dst = torch.zeros((y1 - y0, w, 3), dtype=torch.uint8, device="cuda")
+        st = vip.Strip(s0, s1 - s0, y0, y0, y1 - y0)
+        (f.execute_strip if kind == "abf" else f.bilateral_filter_strip)(dev(img[s0:s1]), d_dst, st)
+        torch.cuda.synchronize()
+        assert np.array_equal(d_dst.cpu().numpy(), got[y0:y1])
+    # a filter output is a convex combination of window pixels: bounded by the local min / max
+    assert got.min() >= img.min() and got.max() <= img.max()
+
+
+def test_full_size_btf_4k_properties(vip):
+    w, h = 3840, 2160
+    tile = O.smooth_image(256, 216, seed=8)
+    img = np.tile(tile, (10, 15, 1))
+    got = run_btf(vip, img, 9, 3)
+    band = 140                                   # > 3 * 17 rows of dependence + window
+    top = O.o_btf(np.ascontiguousarray(img[:band + 60]), 9, 3)[:band - 60]
+    # rows far from the cut depend only on rows inside the crop
+    assert np.array_equal(got[:band - 60][:, :], top[:, :])
+    # periodic input (period 256 x 216) -> periodic output away from the borders
+    assert np.array_equal(got[216:432, 256:512], got[432:648, 512:768])

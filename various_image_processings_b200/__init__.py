@@ -1,0 +1,17 @@
+"""B200-native edge-preserving filters: bilateral, joint/adaptive bilateral, bilateral texture filter.
+
+Drop-in for the CUDA classes of yuyuyu-bot/various_image_processings (include/cuda/*.hpp): the compute lives in
+lib/libvip_b200.so (hand-written sm_100a kernels behind the C ABI of include/vip_c_api.h); this package is the
+Python mirror of the reference's host interface.  There is no CPU fallback.
+"""
+from . import capi
+from .capi import Strip, VipError, launch_count
+from .filters import (CudaAdaptiveBilateralFilter, CudaBilateralFilter, CudaBilateralTextureFilter, CudaIntegralImage,
+                      DeviceImage, MultiGpuFilter, PinnedBuffer, cuda_gradient, cuda_gradient_strip,
+                      device_synchronize)
+
+__all__ = [
+    "capi", "Strip", "VipError", "launch_count", "CudaAdaptiveBilateralFilter", "CudaBilateralFilter",
+    "CudaBilateralTextureFilter", "CudaIntegralImage", "DeviceImage", "MultiGpuFilter", "PinnedBuffer",
+    "cuda_gradient", "cuda_gradient_strip", "device_synchronize",
+]

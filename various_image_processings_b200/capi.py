@@ -1,0 +1,123 @@
+"""ctypes binding of libvip_b200.so (the C ABI declared in include/vip_c_api.h).
+
+The library is the product: there is NO Python / CPU fallback.  Importing this module without a built
+library raises; calling a compute entry point without a CUDA device returns a CUDA error status which is
+turned into VipError.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libvip_b200.so")
+
+VIP_OK = 0
+VIP_LUT_CUDA, VIP_LUT_CPU = 0, 1
+VIP_MG_BF, VIP_MG_ABF, VIP_MG_BTF = 0, 1, 2
+
+
+class VipError(RuntimeError):
+    def __init__(self, status, what):
+        self.status = status
+        super().__init__(f"{what}: {status_string(status)} (status {status})")
+
+
+class Strip(C.Structure):
+    """struct vip_strip: rows held by the buffers and rows to produce (all in full-image row numbers)."""
+    _fields_ = [("src_y0", C.c_int), ("src_rows", C.c_int), ("dst_y0", C.c_int), ("out_y0", C.c_int),
+                ("out_rows", C.c_int)]
+
+
+_vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+_pp = C.POINTER(C.c_void_p)
+
+# name -> (restype, argtypes); this table is also what tests/test_abi.py checks against include/vip_c_api.h
+SIGNATURES = {
+    "vip_version": (C.c_char_p, []),
+    "vip_status_string": (C.c_char_p, [_i]),
+    "vip_launch_count": (C.c_ulonglong, []),
+    "vip_image_create": (_i, [_pp, _i, _i, _i, _i]),
+    "vip_image_destroy": (_i, [_vp]),
+    "vip_image_upload": (_i, [_vp, _vp]),
+    "vip_image_download": (_i, [_vp, _vp]),
+    "vip_image_upload_async": (_i, [_vp, _vp, _vp]),
+    "vip_image_download_async": (_i, [_vp, _vp, _vp]),
+    "vip_image_data": (_vp, [_vp]),
+    "vip_image_bytes": (_sz, [_vp]),
+    "vip_host_alloc": (_i, [_pp, _sz]),
+    "vip_host_free": (_i, [_vp]),
+    "vip_stream_synchronize": (_i, [_vp]),
+    "vip_device_synchronize": (_i, []),
+    "vip_bf_create": (_i, [_pp, _i, _i, _i, _f, _f]),
+    "vip_bf_create_ex": (_i, [_pp, _i, _i, _i, _f, _f, _i]),
+    "vip_bf_destroy": (_i, [_vp]),
+    "vip_bf_run": (_i, [_vp, _vp, _vp, _vp]),
+    "vip_jbf_run": (_i, [_vp, _vp, _vp, _vp, _vp]),
+    "vip_bf_run_strip": (_i, [_vp, _vp, _vp, C.POINTER(Strip), _vp]),
+    "vip_jbf_run_strip": (_i, [_vp, _vp, _vp, _vp, C.POINTER(Strip), _vp]),
+    "vip_bf_halo_rows": (_i, [_vp]),
+    "vip_bf_get_luts": (_i, [_vp, _vp, _vp]),
+    "vip_abf_create": (_i, [_pp, _i, _i, _i, _f, _f]),
+    "vip_abf_create_ex": (_i, [_pp, _i, _i, _i, _f, _f, _i]),
+    "vip_abf_destroy": (_i, [_vp]),
+    "vip_abf_run": (_i, [_vp, _vp, _vp, _vp]),
+    "vip_abf_run_strip": (_i, [_vp, _vp, _vp, C.POINTER(Strip), _vp]),
+    "vip_abf_halo_rows": (_i, [_vp]),
+    "vip_gradient_u8": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "vip_gradient_f32": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "vip_gradient_u8_strip": (_i, [_vp, _vp, _i, _i, _i, C.POINTER(Strip), _vp]),
+    "vip_integral_u8c3": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "vip_integral_get_u8c3": (_i, [_vp, _i, _i, _i, _vp, _i, _vp, _vp]),
+    "vip_integral_table_elems": (_sz, [_i, _i, _i]),
+    "vip_integral_box_mean_u8c3": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "vip_btf_create": (_i, [_pp, _i, _i, _i, _i]),
+    "vip_btf_destroy": (_i, [_vp]),
+    "vip_btf_run": (_i, [_vp, _vp, _vp, _vp]),
+    "vip_btf_blur_rtv": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "vip_btf_guide": (_i, [_vp, _vp, _vp, _vp, _vp]),
+    "vip_btf_halo_rows_per_iteration": (_i, [_vp]),
+    "vip_btf_iterate_strip": (_i, [_vp, _vp, _vp, C.POINTER(Strip), _vp]),
+    "vip_btf_scratch_bytes": (_sz, [_vp]),
+    "vip_mg_create": (_i, [_pp, C.POINTER(C.c_int), _i, _i, _i, _i, _i, _f, _f, _i]),
+    "vip_mg_destroy": (_i, [_vp]),
+    "vip_mg_strip_rows": (_i, [_vp, _i, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "vip_mg_scatter_host": (_i, [_vp, _vp]),
+    "vip_mg_scatter_device": (_i, [_vp, _vp]),
+    "vip_mg_run": (_i, [_vp]),
+    "vip_mg_run_async": (_i, [_vp]),
+    "vip_mg_wait": (_i, [_vp]),
+    "vip_mg_gather_host": (_i, [_vp, _vp]),
+    "vip_mg_last_run_ms": (_i, [_vp, C.POINTER(C.c_float)]),
+    "vip_mg_run_batch_host": (_i, [_vp, _vp, _vp, _i]),
+}
+
+_lib = None
+
+
+def lib():
+    """The loaded library (loads on first use; raises if it has not been built)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "or `make -C various_image_processings_b200/csrc`. There is no CPU fallback.")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def status_string(status):
+    return lib().vip_status_string(int(status)).decode()
+
+
+def check(status, what="vip call"):
+    if status != VIP_OK:
+        raise VipError(status, what)
+
+
+def launch_count():
+    return int(lib().vip_launch_count())

@@ -1,0 +1,381 @@
+// Multi-GPU driver (new layer; the reference is single-GPU).  One host process drives the devices
+// of one box:
+//   * a large image is cut into contiguous row strips, one per device slot; every strip buffer carries `halo`
+//     rows of its neighbours on each side; kernels clamp against the FULL image, so the strip results are
+//     bit-identical to a single-GPU run;
+//   * BF / ABF need their halo once (it comes with the scatter); BTF refreshes 17 halo rows (k = 9) of the new
+//     iterate after every iteration: the receiving device's stream waits for the neighbour's "iteration done"
+//     event and then pulls the rows with cudaMemcpyPeerAsync (NVLink P2P when peer access is enabled), so the
+//     exchange is ordered by events only -- no host synchronisation inside the iteration loop;
+//   * frame batches are dealt round-robin to the devices, two in-flight slots per device so that the upload of
+//     frame i+1 and the download of frame i-1 overlap the kernels of frame i; no inter-device traffic.
+// The same device id may appear several times in the list ("virtual" devices): the strip logic is then
+// exercised on a single GPU.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "../../include/vip_c_api.h"
+#include "vip_internal.h"
+
+extern "C" int vip_btf_create_rows_internal(vip_btf** out, int width, int height, int ksize, int nitr,
+                                            int scratch_rows);
+
+namespace {
+
+inline int cu(cudaError_t e) { return static_cast<int>(e); }
+
+struct Slot {
+    int device = 0;
+    int y0 = 0, rows = 0;      // owned rows
+    int sy0 = 0, srows = 0;    // rows held by the strip buffers (owned + halos, clipped)
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+    std::vector<cudaEvent_t> ev_iter;  // BTF: iterate `it` is complete on this slot
+    uint8_t* src = nullptr;            // rows [sy0, sy0+srows)
+    uint8_t* buf[2] = {nullptr, nullptr};  // BF/ABF: buf[0] = dst (owned rows only); BTF: ping/pong over [sy0, ..)
+    vip_bf* bf = nullptr;
+    vip_abf* abf = nullptr;
+    vip_btf* btf = nullptr;
+    // batch mode (whole frames): two in-flight lanes
+    cudaStream_t bstream[2] = {nullptr, nullptr};
+    uint8_t* bsrc[2] = {nullptr, nullptr};
+    uint8_t* bdst[2] = {nullptr, nullptr};
+    vip_btf* bbtf[2] = {nullptr, nullptr};
+};
+
+}  // namespace
+
+struct vip_mg {
+    int n = 0, kind = 0, width = 0, height = 0, ksize = 0, nitr = 0, halo = 0;
+    float ss = 0.f, sc = 0.f;
+    int result_buf = 0;  // BTF: which of buf[0/1] holds the final iterate (-1: src)
+    bool batch_ready = false;
+    std::vector<Slot> slots;
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = 0;
+    DeviceGuard() { cudaGetDevice(&prev); }
+    ~DeviceGuard() { cudaSetDevice(prev); }
+};
+
+int free_slot(vip_mg* m, Slot& s) {
+    cudaSetDevice(s.device);
+    if (s.bf) vip_bf_destroy(s.bf);
+    if (s.abf) vip_abf_destroy(s.abf);
+    if (s.btf) vip_btf_destroy(s.btf);
+    for (int i = 0; i < 2; i++) {
+        if (s.bbtf[i]) vip_btf_destroy(s.bbtf[i]);
+        if (s.bsrc[i]) cudaFree(s.bsrc[i]);
+        if (s.bdst[i]) cudaFree(s.bdst[i]);
+        if (s.bstream[i]) cudaStreamDestroy(s.bstream[i]);
+        if (s.buf[i]) cudaFree(s.buf[i]);
+    }
+    if (s.src) cudaFree(s.src);
+    for (cudaEvent_t e : s.ev_iter) cudaEventDestroy(e);
+    if (s.ev_start) cudaEventDestroy(s.ev_start);
+    if (s.ev_stop) cudaEventDestroy(s.ev_stop);
+    if (s.stream) cudaStreamDestroy(s.stream);
+    (void)m;
+    return VIP_OK;
+}
+
+int run_one(vip_mg* m, Slot& s, const uint8_t* src, uint8_t* dst, const vip_strip& st) {
+    switch (m->kind) {
+        case VIP_MG_BF: return vip_bf_run_strip(s.bf, src, dst, &st, s.stream);
+        case VIP_MG_ABF: return vip_abf_run_strip(s.abf, src, dst, &st, s.stream);
+        default: return VIP_E_UNSUPPORTED;
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int vip_mg_create(vip_mg** out, const int* device_ids, int n_devices, int kind, int width, int height, int ksize,
+                  float sigma_space, float sigma_color, int nitr) {
+    if (!out || !device_ids) return VIP_E_NULL;
+    *out = nullptr;
+    if (n_devices < 1 || n_devices > 64) return VIP_E_DEVICE;
+    if (kind != VIP_MG_BF && kind != VIP_MG_ABF && kind != VIP_MG_BTF) return VIP_E_UNSUPPORTED;
+    if (width <= 0 || height <= 0) return VIP_E_SIZE;
+    if (ksize < 1 || (ksize & 1) == 0) return VIP_E_KSIZE;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess) return cu(e);
+    for (int i = 0; i < n_devices; i++)
+        if (device_ids[i] < 0 || device_ids[i] >= ndev) return VIP_E_DEVICE;
+    const int halo = (kind == VIP_MG_BTF) ? (ksize - 1) + 2 * (ksize / 2) + 1 : ksize / 2;
+    // every strip must be able to serve a neighbour's halo from its own rows
+    if (n_devices > 1 && height / n_devices < halo) return VIP_E_SIZE;
+
+    DeviceGuard guard;
+    vip_mg* m = new (std::nothrow) vip_mg();
+    if (!m) return VIP_E_ALLOC;
+    m->n = n_devices;
+    m->kind = kind;
+    m->width = width;
+    m->height = height;
+    m->ksize = ksize;
+    m->nitr = nitr;
+    m->halo = halo;
+    m->ss = sigma_space;
+    m->sc = sigma_color;
+    m->slots.resize(n_devices);
+    int rc = VIP_OK;
+    const size_t row_bytes = static_cast<size_t>(width) * 3;
+    for (int i = 0; i < n_devices && rc == VIP_OK; i++) {
+        Slot& s = m->slots[i];
+        s.device = device_ids[i];
+        s.y0 = static_cast<int>(static_cast<long long>(height) * i / n_devices);
+        s.rows = static_cast<int>(static_cast<long long>(height) * (i + 1) / n_devices) - s.y0;
+        s.sy0 = std::max(0, s.y0 - halo);
+        s.srows = std::min(height, s.y0 + s.rows + halo) - s.sy0;
+        if ((e = cudaSetDevice(s.device)) != cudaSuccess) { rc = cu(e); break; }
+        // P2P with the neighbouring slots (an error only means "already enabled" or "not supported":
+        // cudaMemcpyPeerAsync then falls back to staging through the host)
+        for (int j = i - 1; j <= i + 1; j += 2) {
+            if (j < 0 || j >= n_devices || device_ids[j] == s.device) continue;
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, s.device, device_ids[j]) == cudaSuccess && can) {
+                cudaDeviceEnablePeerAccess(device_ids[j], 0);
+                cudaGetLastError();
+            }
+        }
+        if ((e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = cu(e); break; }
+        if ((e = cudaEventCreate(&s.ev_start)) != cudaSuccess) { rc = cu(e); break; }
+        if ((e = cudaEventCreate(&s.ev_stop)) != cudaSuccess) { rc = cu(e); break; }
+        if ((e = cudaMalloc(reinterpret_cast<void**>(&s.src), row_bytes * s.srows)) != cudaSuccess) { rc = cu(e); break; }
+        if (kind == VIP_MG_BTF) {
+            for (int b = 0; b < 2; b++)
+                if ((e = cudaMalloc(reinterpret_cast<void**>(&s.buf[b]), row_bytes * s.srows)) != cudaSuccess) break;
+            if (e != cudaSuccess) { rc = cu(e); break; }
+            s.ev_iter.resize(std::max(nitr, 1));
+            for (auto& ev : s.ev_iter)
+                if ((e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) break;
+            if (e != cudaSuccess) { rc = cu(e); break; }
+            rc = vip_btf_create_rows_internal(&s.btf, width, height, ksize, nitr, s.srows);
+        } else {
+            if ((e = cudaMalloc(reinterpret_cast<void**>(&s.buf[0]), row_bytes * s.rows)) != cudaSuccess) { rc = cu(e); break; }
+            if (kind == VIP_MG_BF) rc = vip_bf_create(&s.bf, width, height, ksize, sigma_space, sigma_color);
+            else rc = vip_abf_create(&s.abf, width, height, ksize, sigma_space, sigma_color);
+        }
+    }
+    if (rc != VIP_OK) {
+        vip_mg_destroy(m);
+        return rc;
+    }
+    *out = m;
+    return VIP_OK;
+}
+
+int vip_mg_destroy(vip_mg* m) {
+    if (!m) return VIP_OK;
+    DeviceGuard guard;
+    for (Slot& s : m->slots) free_slot(m, s);
+    delete m;
+    return VIP_OK;
+}
+
+int vip_mg_strip_rows(const vip_mg* m, int i, int* y0, int* rows) {
+    if (!m) return VIP_E_NULL;
+    if (i < 0 || i >= m->n) return VIP_E_DEVICE;
+    if (y0) *y0 = m->slots[i].y0;
+    if (rows) *rows = m->slots[i].rows;
+    return VIP_OK;
+}
+
+int vip_mg_scatter_host(vip_mg* m, const uint8_t* h_src) {
+    if (!m || !h_src) return VIP_E_NULL;
+    DeviceGuard guard;
+    const size_t row_bytes = static_cast<size_t>(m->width) * 3;
+    for (Slot& s : m->slots) {
+        cudaError_t e = cudaSetDevice(s.device);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(s.src, h_src + row_bytes * s.sy0, row_bytes * s.srows, cudaMemcpyHostToDevice, s.stream);
+        if (e != cudaSuccess) return cu(e);
+    }
+    return VIP_OK;
+}
+
+int vip_mg_scatter_device(vip_mg* m, const uint8_t* d_src_on_dev0) {
+    if (!m || !d_src_on_dev0) return VIP_E_NULL;
+    DeviceGuard guard;
+    const size_t row_bytes = static_cast<size_t>(m->width) * 3;
+    const int dev0 = m->slots[0].device;
+    for (Slot& s : m->slots) {
+        cudaError_t e = cudaSetDevice(s.device);
+        if (e == cudaSuccess)
+            e = cudaMemcpyPeerAsync(s.src, s.device, d_src_on_dev0 + row_bytes * s.sy0, dev0, row_bytes * s.srows, s.stream);
+        if (e != cudaSuccess) return cu(e);
+    }
+    return VIP_OK;
+}
+
+int vip_mg_run_async(vip_mg* m) {
+    if (!m) return VIP_E_NULL;
+    DeviceGuard guard;
+    const size_t row_bytes = static_cast<size_t>(m->width) * 3;
+    cudaError_t e;
+    for (Slot& s : m->slots) {
+        if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
+        if ((e = cudaEventRecord(s.ev_start, s.stream)) != cudaSuccess) return cu(e);
+    }
+    if (m->kind != VIP_MG_BTF) {
+        for (Slot& s : m->slots) {
+            if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
+            const vip_strip st{s.sy0, s.srows, s.y0, s.y0, s.rows};
+            const int rc = run_one(m, s, s.src, s.buf[0], st);
+            if (rc != VIP_OK) return rc;
+        }
+    } else {
+        m->result_buf = -1;
+        for (int it = 0; it < m->nitr; it++) {
+            const int ob = it & 1;
+            for (Slot& s : m->slots) {
+                if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
+                const uint8_t* in = (it == 0) ? s.src : s.buf[ob ^ 1];
+                const vip_strip st{s.sy0, s.srows, s.sy0, s.y0, s.rows};
+                const int rc = vip_btf_iterate_strip(s.btf, in, s.buf[ob], &st, s.stream);
+                if (rc != VIP_OK) return rc;
+                if ((e = cudaEventRecord(s.ev_iter[it], s.stream)) != cudaSuccess) return cu(e);
+            }
+            if (it + 1 < m->nitr) {
+                // halo refresh of the new iterate: pull the rows [sy0, y0) from the slot above and
+                // [y0+rows, sy0+srows) from the slot below, on the RECEIVER's stream
+                for (int i = 0; i < m->n; i++) {
+                    Slot& s = m->slots[i];
+                    if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
+                    if (i > 0 && s.y0 > s.sy0) {
+                        Slot& up = m->slots[i - 1];
+                        if ((e = cudaStreamWaitEvent(s.stream, up.ev_iter[it], 0)) != cudaSuccess) return cu(e);
+                        e = cudaMemcpyPeerAsync(s.buf[ob], s.device, up.buf[ob] + row_bytes * (s.sy0 - up.sy0), up.device,
+                                                row_bytes * (s.y0 - s.sy0), s.stream);
+                        if (e != cudaSuccess) return cu(e);
+                    }
+                    const int below0 = s.y0 + s.rows, below1 = s.sy0 + s.srows;
+                    if (i + 1 < m->n && below1 > below0) {
+                        Slot& dn = m->slots[i + 1];
+                        if ((e = cudaStreamWaitEvent(s.stream, dn.ev_iter[it], 0)) != cudaSuccess) return cu(e);
+                        e = cudaMemcpyPeerAsync(s.buf[ob] + row_bytes * (below0 - s.sy0), s.device,
+                                                dn.buf[ob] + row_bytes * (below0 - dn.sy0), dn.device,
+                                                row_bytes * (below1 - below0), s.stream);
+                        if (e != cudaSuccess) return cu(e);
+                    }
+                }
+            }
+            m->result_buf = ob;
+        }
+    }
+    for (Slot& s : m->slots) {
+        if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
+        if ((e = cudaEventRecord(s.ev_stop, s.stream)) != cudaSuccess) return cu(e);
+    }
+    return VIP_OK;
+}
+
+int vip_mg_wait(vip_mg* m) {
+    if (!m) return VIP_E_NULL;
+    DeviceGuard guard;
+    for (Slot& s : m->slots) {
+        cudaError_t e = cudaSetDevice(s.device);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
+        if (e != cudaSuccess) return cu(e);
+    }
+    return VIP_OK;
+}
+
+int vip_mg_run(vip_mg* m) {
+    const int rc = vip_mg_run_async(m);
+    if (rc != VIP_OK) return rc;
+    return vip_mg_wait(m);
+}
+
+int vip_mg_gather_host(vip_mg* m, uint8_t* h_dst) {
+    if (!m || !h_dst) return VIP_E_NULL;
+    DeviceGuard guard;
+    const size_t row_bytes = static_cast<size_t>(m->width) * 3;
+    for (Slot& s : m->slots) {
+        cudaError_t e = cudaSetDevice(s.device);
+        if (e != cudaSuccess) return cu(e);
+        const uint8_t* from;
+        if (m->kind != VIP_MG_BTF) from = s.buf[0];
+        else if (m->result_buf < 0) from = s.src + row_bytes * (s.y0 - s.sy0);
+        else from = s.buf[m->result_buf] + row_bytes * (s.y0 - s.sy0);
+        e = cudaMemcpyAsync(h_dst + row_bytes * s.y0, from, row_bytes * s.rows, cudaMemcpyDeviceToHost, s.stream);
+        if (e != cudaSuccess) return cu(e);
+    }
+    return vip_mg_wait(m);
+}
+
+int vip_mg_last_run_ms(const vip_mg* m, float* ms) {
+    if (!m || !ms) return VIP_E_NULL;
+    DeviceGuard guard;
+    float worst = 0.f;
+    for (const Slot& s : m->slots) {
+        cudaError_t e = cudaSetDevice(s.device);
+        float t = 0.f;
+        if (e == cudaSuccess) e = cudaEventSynchronize(s.ev_stop);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&t, s.ev_start, s.ev_stop);
+        if (e != cudaSuccess) return cu(e);
+        worst = std::max(worst, t);
+    }
+    *ms = worst;
+    return VIP_OK;
+}
+
+int vip_mg_run_batch_host(vip_mg* m, const uint8_t* h_src, uint8_t* h_dst, int n_frames) {
+    if (!m || !h_src || !h_dst) return VIP_E_NULL;
+    if (n_frames < 0) return VIP_E_SIZE;
+    DeviceGuard guard;
+    const size_t frame_bytes = static_cast<size_t>(m->width) * m->height * 3;
+    cudaError_t e;
+    if (!m->batch_ready) {
+        for (Slot& s : m->slots) {
+            if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
+            for (int l = 0; l < 2; l++) {
+                if ((e = cudaStreamCreateWithFlags(&s.bstream[l], cudaStreamNonBlocking)) != cudaSuccess) return cu(e);
+                if ((e = cudaMalloc(reinterpret_cast<void**>(&s.bsrc[l]), frame_bytes)) != cudaSuccess) return cu(e);
+                if ((e = cudaMalloc(reinterpret_cast<void**>(&s.bdst[l]), frame_bytes)) != cudaSuccess) return cu(e);
+                if (m->kind == VIP_MG_BTF) {
+                    const int rc = vip_btf_create(&s.bbtf[l], m->width, m->height, m->ksize, m->nitr);
+                    if (rc != VIP_OK) return rc;
+                }
+            }
+        }
+        m->batch_ready = true;
+    }
+    std::vector<int> next_lane(m->n, 0);
+    for (int f = 0; f < n_frames; f++) {
+        const int i = f % m->n;
+        Slot& s = m->slots[i];
+        const int l = next_lane[i];
+        next_lane[i] ^= 1;
+        if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
+        cudaStream_t st = s.bstream[l];
+        if ((e = cudaMemcpyAsync(s.bsrc[l], h_src + frame_bytes * f, frame_bytes, cudaMemcpyHostToDevice, st)) !=
+            cudaSuccess)
+            return cu(e);
+        int rc;
+        if (m->kind == VIP_MG_BF) rc = vip_bf_run(s.bf, s.bsrc[l], s.bdst[l], st);
+        else if (m->kind == VIP_MG_ABF) rc = vip_abf_run(s.abf, s.bsrc[l], s.bdst[l], st);
+        else rc = vip_btf_run(s.bbtf[l], s.bsrc[l], s.bdst[l], st);
+        if (rc != VIP_OK) return rc;
+        if ((e = cudaMemcpyAsync(h_dst + frame_bytes * f, s.bdst[l], frame_bytes, cudaMemcpyDeviceToHost, st)) !=
+            cudaSuccess)
+            return cu(e);
+    }
+    for (Slot& s : m->slots) {
+        if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
+        for (int l = 0; l < 2; l++)
+            if ((e = cudaStreamSynchronize(s.bstream[l])) != cudaSuccess) return cu(e);
+    }
+    return VIP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,466 @@
+// Bilateral-family stencil kernels for sm_100a: bilateral (BF), joint bilateral (JBF) and adaptive bilateral
+// (ABF) filters.  Replaces the reference's bilateral_filter_kernel / joint_bilateral_filter_kernel
+// (src/bilateral_filter_impl.cu:7-96, 98-202) and adaptive_bilateral_filter_kernel
+// (src/adaptive_bilateral_filter_impl.cu:7-115).  New design, no code shared with the reference:
+//
+//  * persistent CTAs (2 per SM, 256 threads) stride over 8P x 32 output tiles; a CTA stages the tile plus its
+//    radius halo ONCE as packed 32-bit pixels (B | G<<8 | R<<16; JBF: {guide, src} pairs) in shared memory,
+//    so a tap is one VABSDIFF4.U8.ACC instead of six byte loads and three abs;
+//  * a lane owns one image ROW of the warp's P x 32 sub-tile and P horizontally adjacent outputs: with an odd
+//    tile pitch all 32 lanes hit distinct banks, and one neighbour load + 3 I2F.U8 feeds up to P taps;
+//  * the range LUT is replicated 32x in shared memory (entry i of lane l at word 32*i + l) so the
+//    data-dependent gather is bank-conflict free for ANY image content (random data would otherwise
+//    serialise ~3.5x);
+//  * the zero-weight taps of the circular mask are never issued: every window row is dispatched to a
+//    compile-time half-width variant (bit-neutral: the reference adds +0.0f for them);
+//  * accumulation order and rounding are those of the reference kernel: raster order, w = ks * lut (one
+//    rounding), fmaf(I, w, sum) per channel, sumk += w, IEEE divide, +0.5f, truncate.  Hence the output is
+//    bit-identical to the reference's CUDA build, not merely within 1 LSB.
+//
+// ABF: the k x k box mean comes from exact integer sliding sums over the shared tile (the reference brute
+// forces k^2 float adds of integers, which is the same value); the range index is
+// (int)(|d0|+|d1|+|d2|), d = (q - p) - offset, in the reference's fp32 operation order.
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "vip_internal.h"
+
+namespace vip {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kTileRows = 32;  // one lane per output row
+constexpr int kMaxTiledRadius = 15;
+
+template <int MODE>
+struct Elem {
+    using type = std::uint32_t;
+};
+template <>
+struct Elem<kJBF> {
+    using type = uint2;  // x = guide pixel, y = src pixel
+};
+
+template <int MODE, int P>
+struct Acc {
+    float s0[P], s1[P], s2[P], sk[P];
+    std::uint32_t c[P];             // BF/JBF: packed centre (range source)
+    float fp[MODE == kABF ? 3 : 1][P];   // ABF: centre as float
+    float off[MODE == kABF ? 3 : 1][P];  // ABF: centre - box mean
+};
+
+__device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+__device__ __forceinline__ std::uint32_t load_packed(const std::uint8_t* __restrict__ p) {
+    return static_cast<std::uint32_t>(__ldg(p)) | (static_cast<std::uint32_t>(__ldg(p + 1)) << 8) |
+           (static_cast<std::uint32_t>(__ldg(p + 2)) << 16);
+}
+
+// One window row with half width HW (taps kx in [-HW, HW]) for the P outputs of this thread.
+// trow points at the tile element of pixel (x_first_output - HW) in the window row.
+template <int MODE, int P, int HW, bool CLAMP>
+__device__ __forceinline__ void do_row(const typename Elem<MODE>::type* __restrict__ trow,
+                                       const float* __restrict__ wrow, const float* __restrict__ lutl,
+                                       const std::uint32_t clamp_i, const float clamp_f, Acc<MODE, P>& A) {
+    float w[HW + 1];
+#pragma unroll
+    for (int d = 0; d <= HW; ++d) w[d] = wrow[d];
+#pragma unroll
+    for (int n = 0; n < P + 2 * HW; ++n) {
+        std::uint32_t q, v;
+        if constexpr (MODE == kJBF) {
+            const uint2 e = trow[n];
+            q = e.x;
+            v = e.y;
+        } else {
+            q = trow[n];
+            v = q;
+        }
+        const float f0 = static_cast<float>(v & 0xffu);
+        const float f1 = static_cast<float>((v >> 8) & 0xffu);
+        const float f2 = static_cast<float>((v >> 16) & 0xffu);
+#pragma unroll
+        for (int i = 0; i < P; ++i) {
+            const int kx = n - HW - i;
+            if (kx >= -HW && kx <= HW) {
+                const int d = kx < 0 ? -kx : kx;
+                float l;
+                if constexpr (MODE == kABF) {
+                    // src/adaptive_bilateral_filter_impl.cu:67-73: neighbour - centre - offset, float abs, left-to-right sum
+                    const float d0 = __fsub_rn(__fsub_rn(f0, A.fp[0][i]), A.off[0][i]);
+                    const float d1 = __fsub_rn(__fsub_rn(f1, A.fp[1][i]), A.off[1][i]);
+                    const float d2 = __fsub_rn(__fsub_rn(f2, A.fp[2][i]), A.off[2][i]);
+                    float dist = __fadd_rn(__fadd_rn(fabsf(d0), fabsf(d1)), fabsf(d2));
+                    if constexpr (CLAMP) dist = fminf(dist, clamp_f);
+                    l = lutl[__float2int_rz(dist) * 32];
+                } else {
+                    std::uint32_t sad = __vsadu4(q, A.c[i]);
+                    if constexpr (CLAMP) sad = min(sad, clamp_i);
+                    l = lutl[sad * 32];
+                }
+                const float wt = __fmul_rn(w[d], l);
+                A.s0[i] = __fmaf_rn(f0, wt, A.s0[i]);
+                A.s1[i] = __fmaf_rn(f1, wt, A.s1[i]);
+                A.s2[i] = __fmaf_rn(f2, wt, A.s2[i]);
+                A.sk[i] = __fadd_rn(A.sk[i], wt);
+            }
+        }
+    }
+}
+
+template <int MODE, int P, int RMAX, bool CLAMP>
+__device__ __forceinline__ void dispatch_row(const int hw, const typename Elem<MODE>::type* __restrict__ tcol,
+                                             const float* __restrict__ wrow, const float* __restrict__ lutl,
+                                             const std::uint32_t clamp_i, const float clamp_f, Acc<MODE, P>& A) {
+    // tcol points at the tile element of the FIRST output pixel in the window row.
+#define VIP_ROW_CASE(H)                                                                         \
+    case H:                                                                                     \
+        if constexpr (H <= RMAX) do_row<MODE, P, H, CLAMP>(tcol - H, wrow, lutl, clamp_i, clamp_f, A); \
+        break;
+    switch (hw) {
+        VIP_ROW_CASE(0)
+        VIP_ROW_CASE(1)
+        VIP_ROW_CASE(2)
+        VIP_ROW_CASE(3)
+        VIP_ROW_CASE(4)
+        VIP_ROW_CASE(5)
+        VIP_ROW_CASE(6)
+        VIP_ROW_CASE(7)
+        VIP_ROW_CASE(8)
+        VIP_ROW_CASE(9)
+        VIP_ROW_CASE(10)
+        VIP_ROW_CASE(11)
+        VIP_ROW_CASE(12)
+        VIP_ROW_CASE(13)
+        VIP_ROW_CASE(14)
+        VIP_ROW_CASE(15)
+        default:
+            break;
+    }
+#undef VIP_ROW_CASE
+}
+
+struct SmemLayout {
+    int lut_off, ksw_off, hw_off, tile_off, hs_off, total;
+    int tile_pitch, tile_w, tile_h, hs_pitch;
+};
+
+__host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, int lut_n) {
+    SmemLayout L;
+    const int k = 2 * radius + 1;
+    L.tile_w = kWarps * P + 2 * radius;
+    L.tile_h = kTileRows + 2 * radius;
+    L.tile_pitch = L.tile_w | 1;  // odd: 32 lanes on 32 consecutive rows hit 32 distinct banks
+    L.hs_pitch = (kWarps * P) | 1;
+    int off = 0;
+    L.lut_off = off;
+    off += lut_n * 32 * 4;
+    L.ksw_off = off;
+    off += k * (radius + 1) * 4;
+    L.hw_off = off;
+    off += k * 4;
+    off = (off + 15) & ~15;
+    L.tile_off = off;
+    off += L.tile_pitch * L.tile_h * (mode == kJBF ? 8 : 4);
+    off = (off + 15) & ~15;
+    L.hs_off = off;
+    if (mode == kABF) off += L.hs_pitch * L.tile_h * 8;
+    L.total = off;
+    return L;
+}
+
+template <int MODE, int P, int RMAX, bool CLAMP>
+__global__ void __launch_bounds__(kThreads, 2) stencil_kernel(const StencilArgs a, const int tiles_x, const int n_tiles) {
+    using E = typename Elem<MODE>::type;
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int radius = a.radius;
+    const int k = 2 * radius + 1;
+    const SmemLayout L = make_layout(MODE, P, radius, a.lut_n);
+    float* const lut_s = reinterpret_cast<float*>(smem + L.lut_off);
+    float* const ksw_s = reinterpret_cast<float*>(smem + L.ksw_off);
+    int* const hw_s = reinterpret_cast<int*>(smem + L.hw_off);
+    E* const tile = reinterpret_cast<E*>(smem + L.tile_off);
+    uint2* const hs = reinterpret_cast<uint2*>(smem + L.hs_off);
+
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
+    const int warp = tid >> 5;
+
+    // one-time per CTA: replicated LUT, spatial half rows, half widths
+    for (int i = tid; i < a.lut_n * 32; i += kThreads) lut_s[i] = __ldg(a.lut + (i >> 5));
+    for (int i = tid; i < k * (radius + 1); i += kThreads) ksw_s[i] = __ldg(a.ksw + i);
+    for (int i = tid; i < k; i += kThreads) hw_s[i] = __ldg(a.hw + i);
+
+    const float* const lutl = lut_s + lane;
+    const std::uint32_t clamp_i = static_cast<std::uint32_t>(a.lut_n - 1);
+    const float clamp_f = static_cast<float>(a.lut_n - 1);
+    const int W = a.width, H = a.height;
+    const int tw = L.tile_w, th = L.tile_h, tp = L.tile_pitch;
+    const int step_x = kThreads % tw, step_y = kThreads / tw;
+
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const int tile_x = t % tiles_x, tile_y = t / tiles_x;
+        const int X0 = tile_x * (kWarps * P);
+        const int Y0 = a.out_y0 + tile_y * kTileRows;
+
+        __syncthreads();  // previous tile fully consumed (and, first time round, the tables are written)
+        {
+            int ex = tid % tw, ey = tid / tw;
+            while (ey < th) {
+                const int gx = clampi(X0 - radius + ex, 0, W - 1);
+                const int gy = clampi(Y0 - radius + ey, 0, H - 1) - a.src_y0;
+                const size_t o = (static_cast<size_t>(gy) * W + gx) * 3;
+                if constexpr (MODE == kJBF) {
+                    tile[ey * tp + ex] = make_uint2(load_packed(a.guide + o), load_packed(a.src + o));
+                } else {
+                    tile[ey * tp + ex] = load_packed(a.src + o);
+                }
+                ex += step_x;
+                ey += step_y;
+                if (ex >= tw) {
+                    ex -= tw;
+                    ey += 1;
+                }
+            }
+        }
+        __syncthreads();
+
+        if constexpr (MODE == kABF) {
+            // horizontal k-sums of every tile row for the 8P output columns: hs[row][col] = {B | R<<16, G}
+            const int groups = kWarps * P / 8;
+            for (int item = tid; item < th * groups; item += kThreads) {
+                const int row = item % th, col0 = (item / th) * 8;
+                const std::uint32_t* tr = reinterpret_cast<const std::uint32_t*>(tile) + row * tp + col0;
+                std::uint32_t br = 0, g = 0;
+                for (int j = 0; j < k; ++j) {
+                    const std::uint32_t p = tr[j];
+                    br += p & 0x00ff00ffu;
+                    g += (p >> 8) & 0xffu;
+                }
+                uint2* hr = hs + row * L.hs_pitch + col0;
+                hr[0] = make_uint2(br, g);
+#pragma unroll
+                for (int j = 1; j < 8; ++j) {
+                    const std::uint32_t pn = tr[j + k - 1], po = tr[j - 1];
+                    br += (pn & 0x00ff00ffu) - (po & 0x00ff00ffu);
+                    g += ((pn >> 8) & 0xffu) - ((po >> 8) & 0xffu);
+                    hr[j] = make_uint2(br, g);
+                }
+            }
+            __syncthreads();
+        }
+
+        Acc<MODE, P> A;
+        const E* const tcentre = tile + (lane + radius) * tp + (warp * P + radius);
+#pragma unroll
+        for (int i = 0; i < P; ++i) {
+            A.s0[i] = 0.f;
+            A.s1[i] = 0.f;
+            A.s2[i] = 0.f;
+            A.sk[i] = 0.f;
+            if constexpr (MODE == kJBF) {
+                A.c[i] = tcentre[i].x;
+            } else if constexpr (MODE == kBF) {
+                A.c[i] = tcentre[i];
+            } else {
+                const std::uint32_t c = tcentre[i];
+                A.c[i] = c;
+                std::uint32_t sb = 0, sg = 0, sr = 0;
+                const uint2* hcol = hs + lane * L.hs_pitch + warp * P + i;
+                for (int j = 0; j < k; ++j) {
+                    const uint2 hv = hcol[j * L.hs_pitch];
+                    sb += hv.x & 0xffffu;
+                    sr += hv.x >> 16;
+                    sg += hv.y;
+                }
+                const float kk = static_cast<float>(k * k);
+                const float c0 = static_cast<float>(c & 0xffu), c1 = static_cast<float>((c >> 8) & 0xffu),
+                            c2 = static_cast<float>((c >> 16) & 0xffu);
+                A.fp[0][i] = c0;
+                A.fp[1][i] = c1;
+                A.fp[2][i] = c2;
+                // src/adaptive_bilateral_filter_impl.cu:88-93: centre - sum / (ksize*ksize)
+                A.off[0][i] = __fsub_rn(c0, __fdiv_rn(static_cast<float>(sb), kk));
+                A.off[1][i] = __fsub_rn(c1, __fdiv_rn(static_cast<float>(sg), kk));
+                A.off[2][i] = __fsub_rn(c2, __fdiv_rn(static_cast<float>(sr), kk));
+            }
+        }
+
+#pragma unroll 1
+        for (int ky = -radius; ky <= radius; ++ky) {
+            const int hw = hw_s[ky + radius];
+            dispatch_row<MODE, P, RMAX, CLAMP>(hw, tcentre + ky * tp, ksw_s + (ky + radius) * (radius + 1), lutl, clamp_i,
+                                               clamp_f, A);
+        }
+
+        // epilogue: src/bilateral_filter_impl.cu:93-95
+        const int y = Y0 + lane;
+        const int x0 = X0 + warp * P;
+        if (y < a.out_y0 + a.out_rows && x0 < W) {
+            std::uint8_t o[3 * P];
+#pragma unroll
+            for (int i = 0; i < P; ++i) {
+                o[3 * i + 0] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(A.s0[i], A.sk[i]), 0.5f));
+                o[3 * i + 1] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(A.s1[i], A.sk[i]), 0.5f));
+                o[3 * i + 2] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(A.s2[i], A.sk[i]), 0.5f));
+            }
+            std::uint8_t* const drow = a.dst + (static_cast<size_t>(y - a.dst_y0) * W + x0) * 3;
+            if (x0 + P <= W && (reinterpret_cast<std::uintptr_t>(drow) & 3u) == 0) {
+#pragma unroll
+                for (int j = 0; j < 3 * P / 4; ++j) {
+                    const std::uint32_t wv = o[4 * j] | (o[4 * j + 1] << 8) | (o[4 * j + 2] << 16) |
+                                             (static_cast<std::uint32_t>(o[4 * j + 3]) << 24);
+                    reinterpret_cast<std::uint32_t*>(drow)[j] = wv;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < P; ++i) {
+                    if (x0 + i < W) {
+                        drow[3 * i + 0] = o[3 * i + 0];
+                        drow[3 * i + 1] = o[3 * i + 1];
+                        drow[3 * i + 2] = o[3 * i + 2];
+                    }
+                }
+            }
+        }
+    }
+}
+
+// Any radius, any alignment: one thread per output pixel, straight from global memory.  Same arithmetic
+// and order as the tiled kernels; only used beyond kMaxTiledRadius.
+template <int MODE>
+__global__ void stencil_generic_kernel(const StencilArgs a, const int lut_len) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = a.out_y0 + blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= a.width || y >= a.out_y0 + a.out_rows) return;
+    const int W = a.width, H = a.height, r = a.radius, k = 2 * r + 1;
+    const std::uint8_t* range = (MODE == kJBF) ? a.guide : a.src;
+    const std::uint8_t* cp = range + (static_cast<size_t>(y - a.src_y0) * W + x) * 3;
+    const int c0 = cp[0], c1 = cp[1], c2 = cp[2];
+    float off0 = 0.f, off1 = 0.f, off2 = 0.f;
+    if (MODE == kABF) {
+        int b0 = 0, b1 = 0, b2 = 0;
+        for (int ky = -r; ky <= r; ++ky) {
+            const int yy = clampi(y + ky, 0, H - 1) - a.src_y0;
+            for (int kx = -r; kx <= r; ++kx) {
+                const std::uint8_t* p = a.src + (static_cast<size_t>(yy) * W + clampi(x + kx, 0, W - 1)) * 3;
+                b0 += p[0];
+                b1 += p[1];
+                b2 += p[2];
+            }
+        }
+        const float kk = static_cast<float>(k * k);
+        off0 = __fsub_rn(static_cast<float>(c0), __fdiv_rn(static_cast<float>(b0), kk));
+        off1 = __fsub_rn(static_cast<float>(c1), __fdiv_rn(static_cast<float>(b1), kk));
+        off2 = __fsub_rn(static_cast<float>(c2), __fdiv_rn(static_cast<float>(b2), kk));
+    }
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, sk = 0.f;
+    for (int ky = -r; ky <= r; ++ky) {
+        const int yy = clampi(y + ky, 0, H - 1) - a.src_y0;
+        for (int kx = -r; kx <= r; ++kx) {
+            const float ks = __ldg(a.ks_full + (ky + r) * k + (kx + r));
+            if (ks == 0.f) continue;  // masked corner: the reference adds +0.0f
+            const size_t o = (static_cast<size_t>(yy) * W + clampi(x + kx, 0, W - 1)) * 3;
+            const std::uint8_t* g = range + o;
+            const std::uint8_t* p = a.src + o;
+            int idx;
+            if (MODE == kABF) {
+                const float d0 = __fsub_rn(static_cast<float>(static_cast<int>(g[0]) - c0), off0);
+                const float d1 = __fsub_rn(static_cast<float>(static_cast<int>(g[1]) - c1), off1);
+                const float d2 = __fsub_rn(static_cast<float>(static_cast<int>(g[2]) - c2), off2);
+                idx = __float2int_rz(__fadd_rn(__fadd_rn(fabsf(d0), fabsf(d1)), fabsf(d2)));
+            } else {
+                idx = abs(c0 - g[0]) + abs(c1 - g[1]) + abs(c2 - g[2]);
+            }
+            idx = min(idx, lut_len - 1);
+            const float wt = __fmul_rn(ks, __ldg(a.lut + idx));
+            s0 = __fmaf_rn(static_cast<float>(p[0]), wt, s0);
+            s1 = __fmaf_rn(static_cast<float>(p[1]), wt, s1);
+            s2 = __fmaf_rn(static_cast<float>(p[2]), wt, s2);
+            sk = __fadd_rn(sk, wt);
+        }
+    }
+    std::uint8_t* d = a.dst + (static_cast<size_t>(y - a.dst_y0) * W + x) * 3;
+    d[0] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(s0, sk), 0.5f));
+    d[1] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(s1, sk), 0.5f));
+    d[2] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(s2, sk), 0.5f));
+}
+
+template <int MODE, int P, int RMAX, bool CLAMP>
+cudaError_t launch_tiled(const StencilArgs& a, int sm_count, cudaStream_t stream) {
+    const SmemLayout L = make_layout(MODE, P, a.radius, a.lut_n);
+    auto kern = stencil_kernel<MODE, P, RMAX, CLAMP>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total);
+    if (e != cudaSuccess) return e;
+    const int tiles_x = (a.width + kWarps * P - 1) / (kWarps * P);
+    const int tiles_y = (a.out_rows + kTileRows - 1) / kTileRows;
+    const int n_tiles = tiles_x * tiles_y;
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, L.total);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorInvalidConfiguration;
+    int grid = sm_count * per_sm;
+    if (grid > n_tiles) grid = n_tiles;
+    kern<<<grid, kThreads, L.total, stream>>>(a, tiles_x, n_tiles);
+    count_launch();
+    return cudaGetLastError();
+}
+
+template <int MODE, int P, bool CLAMP>
+cudaError_t launch_by_radius(const StencilArgs& a, int sm_count, cudaStream_t stream) {
+    if (a.radius <= 5) return launch_tiled<MODE, P, 5, CLAMP>(a, sm_count, stream);
+    if (a.radius <= 8) return launch_tiled<MODE, P, 8, CLAMP>(a, sm_count, stream);
+    return launch_tiled<MODE, P, 15, CLAMP>(a, sm_count, stream);
+}
+
+template <int MODE>
+cudaError_t launch_generic(const StencilArgs& a, cudaStream_t stream) {
+    const dim3 block(32, 8);
+    const dim3 grid((a.width + 31) / 32, (a.out_rows + 7) / 8);
+    stencil_generic_kernel<MODE><<<grid, block, 0, stream>>>(a, MODE == kABF ? 1536 : 768);
+    count_launch();
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+int stencil_max_tiled_radius() { return kMaxTiledRadius; }
+
+void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, int* lut_n, int* clamp) {
+    // Two resident CTAs per SM: 2 * (dynamic + 1 KB reserved) <= 228 KB.
+    constexpr int kTwoCtaBudget = (233472 / 2) - 1024;
+    *lut_n = table_len;
+    *clamp = 0;
+    if (radius > kMaxTiledRadius) return;
+    const bool zero_tail = last_nz + 1 < table_len;
+    if (make_layout(mode, 8, radius, table_len).total <= kTwoCtaBudget || !zero_tail) return;
+    *lut_n = last_nz + 2;  // entry last_nz+1 is 0 and stands for every larger index
+    *clamp = 1;
+}
+
+cudaError_t launch_stencil(StencilMode mode, const StencilArgs& a, int sm_count, cudaStream_t stream) {
+    if (a.out_rows <= 0 || a.width <= 0) return cudaSuccess;
+    if (a.radius > kMaxTiledRadius) {
+        switch (mode) {
+            case kBF: return launch_generic<kBF>(a, stream);
+            case kJBF: return launch_generic<kJBF>(a, stream);
+            default: return launch_generic<kABF>(a, stream);
+        }
+    }
+    const bool clamp = a.lut_clamp != 0;
+    switch (mode) {
+        case kBF:
+            return clamp ? launch_by_radius<kBF, 8, true>(a, sm_count, stream)
+                         : launch_by_radius<kBF, 8, false>(a, sm_count, stream);
+        case kJBF:
+            return clamp ? launch_by_radius<kJBF, 8, true>(a, sm_count, stream)
+                         : launch_by_radius<kJBF, 8, false>(a, sm_count, stream);
+        default:
+            return clamp ? launch_by_radius<kABF, 8, true>(a, sm_count, stream)
+                         : launch_by_radius<kABF, 8, false>(a, sm_count, stream);
+    }
+}
+
+}  // namespace vip

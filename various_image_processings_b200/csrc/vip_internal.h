@@ -1,0 +1,65 @@
+// Internal declarations shared by the kernel translation units and the C-ABI layer (capi.cu).
+// Nothing here is visible outside libvip_b200.so.
+#ifndef VIP_INTERNAL_H
+#define VIP_INTERNAL_H
+
+#include <cuda_runtime.h>
+
+#include <cstddef>
+#include <cstdint>
+
+namespace vip {
+
+enum StencilMode { kBF = 0, kJBF = 1, kABF = 2 };
+
+// Arguments of the bilateral-family stencil kernels (stencil.cu).  Row numbers are rows of the FULL image;
+// the buffers hold the rows a strip describes (include/vip_c_api.h, struct vip_strip).
+struct StencilArgs {
+    const std::uint8_t* src;    // values (BF/ABF: also the range source)
+    const std::uint8_t* guide;  // JBF: range source; otherwise unused
+    std::uint8_t* dst;
+    int width, height;          // full image
+    int src_y0, src_rows;       // rows held by src / guide
+    int dst_y0;                 // full-image row of dst's first row
+    int out_y0, out_rows;       // rows to produce
+    int radius;
+    const float* lut;           // device: colour table (768 or 1536 floats)
+    int lut_n;                  // entries replicated into shared memory
+    int lut_clamp;              // 1: index is clamped to lut_n-1 (whose entry, and all after it, is 0)
+    const float* ksw;           // device: (2r+1) x (r+1) half rows of the spatial kernel, ksw[(ky+r)*(r+1)+|kx|]
+    const int* hw;              // device: 2r+1 half widths, hw[ky+r] = floor(sqrt(r^2-ky^2))
+    const float* ks_full;       // device: ksize*ksize spatial kernel (generic fallback)
+};
+
+cudaError_t launch_stencil(StencilMode mode, const StencilArgs& a, int sm_count, cudaStream_t stream);
+// Largest radius the tiled kernels cover; beyond it the generic one-thread-per-pixel kernel runs.
+int stencil_max_tiled_radius();
+// Decides how many colour-table entries are replicated in shared memory and whether the index is clamped.
+void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, int* lut_n, int* clamp);
+
+// gradient.cu
+cudaError_t launch_gradient_u8(const std::uint8_t* src, float* dst, int width, int height, int channels, int src_y0,
+                               int src_rows, int dst_y0, int out_y0, int out_rows, cudaStream_t stream);
+cudaError_t launch_gradient_f32(const float* src, float* dst, int width, int height, int channels,
+                                cudaStream_t stream);
+
+// btf.cu
+cudaError_t launch_blur_rtv(const std::uint8_t* image, const float* magnitude, float* blurred, float* rtv, int width,
+                            int height, int ksize, int src_y0, int src_rows, int dst_y0, int out_y0, int out_rows,
+                            cudaStream_t stream);
+cudaError_t launch_guide(const float* blurred, const float* rtv, std::uint8_t* guide, int width, int height, int ksize,
+                         int src_y0, int src_rows, int dst_y0, int out_y0, int out_rows, cudaStream_t stream);
+
+// integral.cu
+cudaError_t launch_integral_u8c3(const std::uint8_t* src, std::uint32_t* table, int width, int height, int radius,
+                                 cudaStream_t stream);
+cudaError_t launch_integral_get(const std::uint32_t* table, int width, int height, int radius,
+                                const std::int32_t* rects, int n, std::uint32_t* out, cudaStream_t stream);
+cudaError_t launch_integral_box_mean(const std::uint32_t* table, float* mean, int width, int height, int radius,
+                                     cudaStream_t stream);
+
+void count_launch(int n = 1);
+
+}  // namespace vip
+
+#endif
