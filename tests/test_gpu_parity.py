@@ -210,7 +210,19 @@ def test_guide_stage(vip, w, h, k):
     f.compute_guide(dev(blurred), dev(rtv), g)
     torch.cuda.synchronize()
     got = g.cpu().numpy()
-    assert np.array_equal(got, O.o_guide(blurred, rtv, k, O.ARITH_CUDA))
+    # The oracle evaluates alpha with glibc expf, the device with CUDA's expf (ex2.approx based, not restatable
+    # bit-for-bit on a CPU): a 1-ulp difference can flip the truncation of one sample.  Tolerance: <= 1 level on
+    # <= 0.1 % of the samples vs the oracle; EXACT vs the reference's own CUDA kernel when it is built.
+    want = O.o_guide(blurred, rtv, k, O.ARITH_CUDA)
+    assert maxdiff(got, want) <= 1 and (got != want).mean() <= 1e-3
+    if O.have_ref_cuda():
+        R = O.ref_cuda()
+        p = R.refcu_btf_create(w, h, k, 1)
+        g2 = torch.empty_like(g)
+        R.refcu_btf_guide(p, dev(blurred).data_ptr(), dev(rtv).data_ptr(), g2.data_ptr(), w, h)
+        torch.cuda.synchronize()
+        R.refcu_btf_destroy(p)
+        assert torch.equal(g, g2)
     if (w, h, k) == (50, 50, 9):
         # the CPU reference uses glibc expf and unfused multiply-add: at most 1 level, on few pixels
         assert maxdiff(got, G["btf_guide_cpu"]) <= 1

@@ -119,5 +119,12 @@ def check(status, what="vip call"):
         raise VipError(status, what)
 
 
+def release(fn_name, handle):
+    """Destructor helper: frees a handle; silent during interpreter shutdown (module globals already torn down)."""
+    L = _lib
+    if L is not None and handle:
+        getattr(L, fn_name)(handle)
+
+
 def launch_count():
     return int(lib().vip_launch_count())

@@ -57,7 +57,8 @@ class DeviceImage:
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
         if h:
-            lib().vip_image_destroy(h)
+            if capi is not None:
+                capi.release('vip_image_destroy', h)
 
     @property
     def shape(self):
@@ -103,7 +104,8 @@ class PinnedBuffer:
         p, self._p = getattr(self, "_p", None), None
         if p:
             self.array = None
-            lib().vip_host_free(p)
+            if capi is not None:
+                capi.release('vip_host_free', p)
 
 
 class CudaBilateralFilter:
@@ -118,7 +120,8 @@ class CudaBilateralFilter:
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
         if h:
-            lib().vip_bf_destroy(h)
+            if capi is not None:
+                capi.release('vip_bf_destroy', h)
 
     def bilateral_filter(self, d_src, d_dst):
         """Blocking, like the reference (src/bilateral_filter_impl.cu:294-300)."""
@@ -165,7 +168,8 @@ class CudaAdaptiveBilateralFilter:
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
         if h:
-            lib().vip_abf_destroy(h)
+            if capi is not None:
+                capi.release('vip_abf_destroy', h)
 
     def execute(self, d_src, d_dst):
         self.execute_async(d_src, d_dst)
@@ -194,7 +198,8 @@ class CudaBilateralTextureFilter:
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
         if h:
-            lib().vip_btf_destroy(h)
+            if capi is not None:
+                capi.release('vip_btf_destroy', h)
 
     def execute(self, d_src, d_dst):
         self.execute_async(d_src, d_dst)
@@ -280,7 +285,8 @@ class MultiGpuFilter:
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
         if h:
-            lib().vip_mg_destroy(h)
+            if capi is not None:
+                capi.release('vip_mg_destroy', h)
 
     def strip_rows(self, i):
         y0, rows = C.c_int(), C.c_int()
