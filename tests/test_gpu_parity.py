@@ -219,7 +219,8 @@ def test_guide_stage(vip, w, h, k):
         R = O.ref_cuda()
         p = R.refcu_btf_create(w, h, k, 1)
         g2 = torch.empty_like(g)
-        R.refcu_btf_guide(p, dev(blurred).data_ptr(), dev(rtv).data_ptr(), g2.data_ptr(), w, h)
+        d_bl, d_rt = dev(blurred), dev(rtv)          # keep alive across the reference's launch
+        R.refcu_btf_guide(p, d_bl.data_ptr(), d_rt.data_ptr(), g2.data_ptr(), w, h)
         torch.cuda.synchronize()
         R.refcu_btf_destroy(p)
         assert torch.equal(g, g2)
