@@ -1,0 +1,85 @@
+#!/usr/bin/env python
+"""Developer loop on the GPU box: time each kernel of the hot path at BASELINE sizes and check it bit-for-bit against
+the reference's own CUDA kernels (oracle/_ref/libvip_ref_cuda.so -- checker only) on the same random input.
+  python tools/kbench.py [bf:3840x2160:11 abf:3840x2160:15 jbf:3840x2160:17 btf:3840x2160:9 ...]
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import _oracle as O  # noqa: E402
+import various_image_processings_b200 as vip  # noqa: E402
+
+DEFAULT = ["bf:3840x2160:11", "abf:3840x2160:15", "jbf:3840x2160:17", "bf:7680x4320:31", "btf:3840x2160:9", "bf:1920x1080:9", "abf:1920x1080:9"]
+
+
+def taps(r):
+    return sum(1 for y in range(-r, r + 1) for x in range(-r, r + 1) if x * x + y * y <= r * r)
+
+
+def timed(fn, n=10, warm=2):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n
+
+
+def main():
+    R = O.ref_cuda() if O.have_ref_cuda() else None
+    content = os.environ.get("KB_CONTENT", "rand")
+    for spec in (sys.argv[1:] or DEFAULT):
+        kind, size, k = spec.split(":")
+        w, h = map(int, size.split("x"))
+        k = int(k)
+        rs = np.random.RandomState(42)
+        if content == "rand":
+            img = rs.randint(0, 256, size=(h, w, 3)).astype(np.uint8)
+        else:
+            t = O.smooth_image(256, 216, seed=8)
+            img = np.ascontiguousarray(np.tile(t, (h // 216 + 1, w // 256 + 1, 1))[:h, :w])
+        guide = np.ascontiguousarray(img[::-1, ::-1])
+        d_src, d_guide = torch.from_numpy(img).cuda(), torch.from_numpy(guide).cuda()
+        d_dst, d_ref = torch.empty_like(d_src), torch.empty_like(d_src)
+        ref_ms = float("nan")
+        if kind in ("bf", "jbf"):
+            f = vip.CudaBilateralFilter(w, h, k)
+            run = (lambda: f.bilateral_filter_async(d_src, d_dst)) if kind == "bf" else (lambda: f.joint_bilateral_filter_async(d_src, d_guide, d_dst))
+            t_per_px = taps(k // 2)
+            if R:
+                p = R.refcu_bf_create(w, h, k, 10.0, 30.0)
+                rr = (lambda: R.refcu_bf_run(p, d_src.data_ptr(), d_ref.data_ptr())) if kind == "bf" else (lambda: R.refcu_jbf_run(p, d_src.data_ptr(), d_guide.data_ptr(), d_ref.data_ptr()))
+        elif kind == "abf":
+            f = vip.CudaAdaptiveBilateralFilter(w, h, k)
+            run = lambda: f.execute_async(d_src, d_dst)
+            t_per_px = taps(k // 2)
+            if R:
+                p = R.refcu_abf_create(w, h, k, 10.0, 30.0)
+                rr = lambda: R.refcu_abf_run(p, d_src.data_ptr(), d_ref.data_ptr())
+        else:
+            f = vip.CudaBilateralTextureFilter(w, h, k, 3)
+            run = lambda: f.execute_async(d_src, d_dst)
+            t_per_px = 3 * taps(k - 1)
+            if R:
+                p = R.refcu_btf_create(w, h, k, 3)
+                rr = lambda: R.refcu_btf_run(p, d_src.data_ptr(), d_ref.data_ptr())
+        ms = timed(run)
+        same = "n/a"
+        if R:
+            ref_ms = timed(rr, n=2, warm=1)
+            same = "EXACT" if torch.equal(d_dst, d_ref) else "DIFF(%d px)" % int((d_dst != d_ref).any(-1).sum().item())
+        print(f"{spec:22s} {ms:8.3f} ms  {w * h / ms / 1e3:9.0f} Mpix/s  {w * h * t_per_px / ms / 1e6:8.1f} Gtap/s   ref-cuda {ref_ms:9.3f} ms  x{ref_ms / ms:5.1f}  {same}", flush=True)
+
+
+if __name__ == "__main__":
+    main()

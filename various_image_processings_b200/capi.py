@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libvip_b200.so")
+# VIP_B200_LIB: developer override to A/B a differently built library (tools/kbench.py); never a fallback
+LIB_PATH = os.environ.get("VIP_B200_LIB") or os.path.join(_HERE, "lib", "libvip_b200.so")
 
 VIP_OK = 0
 VIP_LUT_CUDA, VIP_LUT_CPU = 0, 1

@@ -7,19 +7,24 @@
 //    radius halo ONCE as packed 32-bit pixels (B | G<<8 | R<<16; JBF: {guide, src} pairs) in shared memory,
 //    so a tap is one VABSDIFF4.U8.ACC instead of six byte loads and three abs;
 //  * a lane owns one image ROW of the warp's P x 32 sub-tile and P horizontally adjacent outputs: with an odd
-//    tile pitch all 32 lanes hit distinct banks, and one neighbour load + 3 I2F.U8 feeds up to P taps;
+//    tile pitch all 32 lanes hit distinct banks, and one neighbour load + unpack feeds up to P taps;
 //  * the range LUT is replicated 32x in shared memory (entry i of lane l at word 32*i + l) so the
 //    data-dependent gather is bank-conflict free for ANY image content (random data would otherwise
 //    serialise ~3.5x);
-//  * the zero-weight taps of the circular mask are never issued: every window row is dispatched to a
-//    compile-time half-width variant (bit-neutral: the reference adds +0.0f for them);
+//  * the zero-weight taps of the circular mask are never issued (bit-neutral: the reference adds +0.0f for
+//    them): a window row of 2*hw+1 taps is cut into runs of 8 taps plus one odd remainder
+//    (7/5/3/1).  Only those five run bodies exist as code (~30 KB for BF), whatever the radius: the first
+//    version unrolled every half width separately and spent more time waiting for instruction fetch than for
+//    anything else (ncu: stall_no_instruction 2.96 per issue at r=15, profiles/r01_*);
 //  * accumulation order and rounding are those of the reference kernel: raster order, w = ks * lut (one
 //    rounding), fmaf(I, w, sum) per channel, sumk += w, IEEE divide, +0.5f, truncate.  Hence the output is
 //    bit-identical to the reference's CUDA build, not merely within 1 LSB.
 //
 // ABF: the k x k box mean comes from exact integer sliding sums over the shared tile (the reference brute
 // forces k^2 float adds of integers, which is the same value); the range index is
-// (int)(|d0|+|d1|+|d2|), d = (q - p) - offset, in the reference's fp32 operation order.
+// (int)(|d0|+|d1|+|d2|), d = (q - p) - offset, in the reference's fp32 operation order.  The truncation is done
+// on the FMA pipe (add 2^23 with round-toward-zero; the mantissa then holds floor(dist) exactly) instead of
+// F2I on the quarter-rate XU pipe.
 #include <cuda_runtime.h>
 
 #include <cstdint>
@@ -43,9 +48,31 @@ struct Elem<kJBF> {
     using type = uint2;  // x = guide pixel, y = src pixel
 };
 
+// Packed fp32x2 (sm_100 FFMA2): {s0,s1} and {s2,sk} accumulate with one instruction each; sk = fma(1, w, sk) is the
+// same rounding as sk + w.  The multiplier w is a scalar operand broadcast to both halves (FFMA2 Rd, Ra.F32x2, Rb.F32, Rd).
+// Measured on B200 (tools/kbench.py): FFMA2 issues at half the FFMA rate, so this only trades issue slots for
+// nothing on the FMA pipe: +3 % for BF/JBF (ALU-pipe heavy), -2 % for ABF (FMA-pipe heavy) -> used for BF/JBF only.
+template <int MODE>
+struct UseFma2 {
+    static constexpr bool value = MODE != kABF;
+};
+__device__ __forceinline__ unsigned long long pack2(const float lo, const float hi) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(const unsigned long long v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ void fma2(unsigned long long& acc, const unsigned long long a, const unsigned long long b) {
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
+}
+
 template <int MODE, int P>
 struct Acc {
-    float s0[P], s1[P], s2[P], sk[P];
+    float s0[UseFma2<MODE>::value ? 1 : P], s1[UseFma2<MODE>::value ? 1 : P], s2[UseFma2<MODE>::value ? 1 : P],
+        sk[UseFma2<MODE>::value ? 1 : P];
+    unsigned long long s01[UseFma2<MODE>::value ? P : 1], s2k[UseFma2<MODE>::value ? P : 1];
     std::uint32_t c[P];             // BF/JBF: packed centre (range source)
     float fp[MODE == kABF ? 3 : 1][P];   // ABF: centre as float
     float off[MODE == kABF ? 3 : 1][P];  // ABF: centre - box mean
@@ -58,35 +85,59 @@ __device__ __forceinline__ std::uint32_t load_packed(const std::uint8_t* __restr
            (static_cast<std::uint32_t>(__ldg(p + 2)) << 16);
 }
 
-// One window row with half width HW (taps kx in [-HW, HW]) for the P outputs of this thread.
-// trow points at the tile element of pixel (x_first_output - HW) in the window row.
-template <int MODE, int P, int HW, bool CLAMP>
-__device__ __forceinline__ void do_row(const typename Elem<MODE>::type* __restrict__ trow,
-                                       const float* __restrict__ wrow, const float* __restrict__ lutl,
-                                       const std::uint32_t clamp_i, const float clamp_f, Acc<MODE, P>& A) {
-    float w[HW + 1];
+__device__ __forceinline__ float lds_f32(const std::uint32_t addr) {
+    float v;
+    asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+
+// u8 -> float: I2F.U8 with a byte selector (one XU-pipe instruction).  The XU-free alternative (PRMT to the bits of
+// 2^23 + byte, then FADD -2^23) costs a second issue slot and measured 3-7 % slower (tools/kbench.py, B200).
+template <int BYTE>
+__device__ __forceinline__ float byte_to_float(const std::uint32_t v) {
+    return static_cast<float>((v >> (8 * BYTE)) & 0xffu);
+}
+
+// A run of L consecutive taps (kx0 .. kx0+L-1) of one window row for the P outputs of this thread.
+// t points at the tile element of (first output, kx0); wp at the L weights of the run (16-byte aligned,
+// readable up to the next multiple of 4).  Per accumulator the taps are visited in increasing kx.
+template <int MODE, int P, int L, bool CLAMP>
+__device__ __forceinline__ void run_taps(const typename Elem<MODE>::type* __restrict__ t, const float* __restrict__ wp,
+                                         const std::uint32_t lut_addr, const std::uint32_t clamp_i, const float clamp_f,
+                                         Acc<MODE, P>& A) {
+    float w[(L + 3) & ~3];
 #pragma unroll
-    for (int d = 0; d <= HW; ++d) w[d] = wrow[d];
+    for (int j = 0; j < (L + 3) / 4; ++j) {
+        const float4 v = reinterpret_cast<const float4*>(wp)[j];
+        w[4 * j + 0] = v.x;
+        w[4 * j + 1] = v.y;
+        w[4 * j + 2] = v.z;
+        w[4 * j + 3] = v.w;
+    }
 #pragma unroll
-    for (int n = 0; n < P + 2 * HW; ++n) {
+    for (int n = 0; n < P + L - 1; ++n) {
         std::uint32_t q, v;
         if constexpr (MODE == kJBF) {
-            const uint2 e = trow[n];
+            const uint2 e = t[n];
             q = e.x;
             v = e.y;
         } else {
-            q = trow[n];
+            q = t[n];
             v = q;
         }
-        const float f0 = static_cast<float>(v & 0xffu);
-        const float f1 = static_cast<float>((v >> 8) & 0xffu);
-        const float f2 = static_cast<float>((v >> 16) & 0xffu);
+        const float f0 = byte_to_float<0>(v);
+        const float f1 = byte_to_float<1>(v);
+        const float f2 = byte_to_float<2>(v);
+        unsigned long long f01 = 0, f21 = 0;
+        if constexpr (UseFma2<MODE>::value) {
+            f01 = pack2(f0, f1);
+            f21 = pack2(f2, 1.f);
+        }
 #pragma unroll
         for (int i = 0; i < P; ++i) {
-            const int kx = n - HW - i;
-            if (kx >= -HW && kx <= HW) {
-                const int d = kx < 0 ? -kx : kx;
-                float l;
+            const int j = n - i;
+            if (j >= 0 && j < L) {
+                std::uint32_t addr;
                 if constexpr (MODE == kABF) {
                     // src/adaptive_bilateral_filter_impl.cu:67-73: neighbour - centre - offset, float abs, left-to-right sum
                     const float d0 = __fsub_rn(__fsub_rn(f0, A.fp[0][i]), A.off[0][i]);
@@ -94,57 +145,49 @@ __device__ __forceinline__ void do_row(const typename Elem<MODE>::type* __restri
                     const float d2 = __fsub_rn(__fsub_rn(f2, A.fp[2][i]), A.off[2][i]);
                     float dist = __fadd_rn(__fadd_rn(fabsf(d0), fabsf(d1)), fabsf(d2));
                     if constexpr (CLAMP) dist = fminf(dist, clamp_f);
-                    l = lutl[__float2int_rz(dist) * 32];
+                    // (int)dist: bits(dist +rz 2^23) = 0x4b000000 + floor(dist); << 7 leaves 0x80000000 + 128*floor(dist),
+                    // and lut_addr already carries the -0x80000000 (32-bit wrap-around)
+                    addr = lut_addr + (__float_as_uint(__fadd_rz(dist, 8388608.f)) << 7);
                 } else {
                     std::uint32_t sad = __vsadu4(q, A.c[i]);
                     if constexpr (CLAMP) sad = min(sad, clamp_i);
-                    l = lutl[sad * 32];
+                    addr = lut_addr + (sad << 7);
                 }
-                const float wt = __fmul_rn(w[d], l);
-                A.s0[i] = __fmaf_rn(f0, wt, A.s0[i]);
-                A.s1[i] = __fmaf_rn(f1, wt, A.s1[i]);
-                A.s2[i] = __fmaf_rn(f2, wt, A.s2[i]);
-                A.sk[i] = __fadd_rn(A.sk[i], wt);
+                const float wt = __fmul_rn(w[j], lds_f32(addr));
+                if constexpr (UseFma2<MODE>::value) {
+                    const unsigned long long ww = pack2(wt, wt);
+                    fma2(A.s01[i], f01, ww);
+                    fma2(A.s2k[i], f21, ww);
+                } else {
+                    A.s0[i] = __fmaf_rn(f0, wt, A.s0[i]);
+                    A.s1[i] = __fmaf_rn(f1, wt, A.s1[i]);
+                    A.s2[i] = __fmaf_rn(f2, wt, A.s2[i]);
+                    A.sk[i] = __fadd_rn(A.sk[i], wt);
+                }
             }
         }
     }
 }
 
-template <int MODE, int P, int RMAX, bool CLAMP>
-__device__ __forceinline__ void dispatch_row(const int hw, const typename Elem<MODE>::type* __restrict__ tcol,
-                                             const float* __restrict__ wrow, const float* __restrict__ lutl,
-                                             const std::uint32_t clamp_i, const float clamp_f, Acc<MODE, P>& A) {
-    // tcol points at the tile element of the FIRST output pixel in the window row.
-#define VIP_ROW_CASE(H)                                                                         \
-    case H:                                                                                     \
-        if constexpr (H <= RMAX) do_row<MODE, P, H, CLAMP>(tcol - H, wrow, lutl, clamp_i, clamp_f, A); \
-        break;
-    switch (hw) {
-        VIP_ROW_CASE(0)
-        VIP_ROW_CASE(1)
-        VIP_ROW_CASE(2)
-        VIP_ROW_CASE(3)
-        VIP_ROW_CASE(4)
-        VIP_ROW_CASE(5)
-        VIP_ROW_CASE(6)
-        VIP_ROW_CASE(7)
-        VIP_ROW_CASE(8)
-        VIP_ROW_CASE(9)
-        VIP_ROW_CASE(10)
-        VIP_ROW_CASE(11)
-        VIP_ROW_CASE(12)
-        VIP_ROW_CASE(13)
-        VIP_ROW_CASE(14)
-        VIP_ROW_CASE(15)
-        default:
-            break;
+// One window row of len = 2*hw+1 taps: runs of 8, then the odd remainder.
+template <int MODE, int P, bool CLAMP>
+__device__ __forceinline__ void do_row(int len, const typename Elem<MODE>::type* __restrict__ t,
+                                       const float* __restrict__ wp, const std::uint32_t lut_addr,
+                                       const std::uint32_t clamp_i, const float clamp_f, Acc<MODE, P>& A) {
+#pragma unroll 1
+    for (; len >= 8; len -= 8, t += 8, wp += 8) run_taps<MODE, P, 8, CLAMP>(t, wp, lut_addr, clamp_i, clamp_f, A);
+    switch (len) {
+        case 7: run_taps<MODE, P, 7, CLAMP>(t, wp, lut_addr, clamp_i, clamp_f, A); break;
+        case 5: run_taps<MODE, P, 5, CLAMP>(t, wp, lut_addr, clamp_i, clamp_f, A); break;
+        case 3: run_taps<MODE, P, 3, CLAMP>(t, wp, lut_addr, clamp_i, clamp_f, A); break;
+        case 1: run_taps<MODE, P, 1, CLAMP>(t, wp, lut_addr, clamp_i, clamp_f, A); break;
+        default: break;
     }
-#undef VIP_ROW_CASE
 }
 
 struct SmemLayout {
-    int lut_off, ksw_off, hw_off, tile_off, hs_off, total;
-    int tile_pitch, tile_w, tile_h, hs_pitch;
+    int lut_off, w_off, hw_off, tile_off, hs_off, total;
+    int tile_pitch, tile_w, tile_h, hs_pitch, w_pitch;
 };
 
 __host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, int lut_n) {
@@ -157,8 +200,9 @@ __host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, i
     int off = 0;
     L.lut_off = off;
     off += lut_n * 32 * 4;
-    L.ksw_off = off;
-    off += k * (radius + 1) * 4;
+    L.w_pitch = (k + 7) & ~7;  // row ky: its 2*hw+1 non-zero weights from index 0, zero padded
+    L.w_off = off;
+    off += k * L.w_pitch * 4;
     L.hw_off = off;
     off += k * 4;
     off = (off + 15) & ~15;
@@ -171,7 +215,7 @@ __host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, i
     return L;
 }
 
-template <int MODE, int P, int RMAX, bool CLAMP>
+template <int MODE, int P, bool CLAMP>
 __global__ void __launch_bounds__(kThreads, 2) stencil_kernel(const StencilArgs a, const int tiles_x, const int n_tiles) {
     using E = typename Elem<MODE>::type;
     extern __shared__ __align__(16) unsigned char smem[];
@@ -179,7 +223,7 @@ __global__ void __launch_bounds__(kThreads, 2) stencil_kernel(const StencilArgs 
     const int k = 2 * radius + 1;
     const SmemLayout L = make_layout(MODE, P, radius, a.lut_n);
     float* const lut_s = reinterpret_cast<float*>(smem + L.lut_off);
-    float* const ksw_s = reinterpret_cast<float*>(smem + L.ksw_off);
+    float* const w_s = reinterpret_cast<float*>(smem + L.w_off);
     int* const hw_s = reinterpret_cast<int*>(smem + L.hw_off);
     E* const tile = reinterpret_cast<E*>(smem + L.tile_off);
     uint2* const hs = reinterpret_cast<uint2*>(smem + L.hs_off);
@@ -190,10 +234,16 @@ __global__ void __launch_bounds__(kThreads, 2) stencil_kernel(const StencilArgs 
 
     // one-time per CTA: replicated LUT, spatial half rows, half widths
     for (int i = tid; i < a.lut_n * 32; i += kThreads) lut_s[i] = __ldg(a.lut + (i >> 5));
-    for (int i = tid; i < k * (radius + 1); i += kThreads) ksw_s[i] = __ldg(a.ksw + i);
+    for (int i = tid; i < k * L.w_pitch; i += kThreads) {
+        const int row = i / L.w_pitch, j = i - row * L.w_pitch;
+        const int hw = __ldg(a.hw + row);
+        w_s[i] = j <= 2 * hw ? __ldg(a.ks_full + row * k + (radius - hw + j)) : 0.f;
+    }
     for (int i = tid; i < k; i += kThreads) hw_s[i] = __ldg(a.hw + i);
 
-    const float* const lutl = lut_s + lane;
+    // byte address of this lane's copy of entry 0; ABF folds the 2^23 bias of its index trick in (see run_taps)
+    const std::uint32_t lut_addr = static_cast<std::uint32_t>(__cvta_generic_to_shared(lut_s + lane)) -
+                                   (MODE == kABF ? 0x80000000u : 0u);
     const std::uint32_t clamp_i = static_cast<std::uint32_t>(a.lut_n - 1);
     const float clamp_f = static_cast<float>(a.lut_n - 1);
     const int W = a.width, H = a.height;
@@ -256,10 +306,15 @@ __global__ void __launch_bounds__(kThreads, 2) stencil_kernel(const StencilArgs 
         const E* const tcentre = tile + (lane + radius) * tp + (warp * P + radius);
 #pragma unroll
         for (int i = 0; i < P; ++i) {
-            A.s0[i] = 0.f;
-            A.s1[i] = 0.f;
-            A.s2[i] = 0.f;
-            A.sk[i] = 0.f;
+            if constexpr (UseFma2<MODE>::value) {
+                A.s01[i] = 0ull;
+                A.s2k[i] = 0ull;
+            } else {
+                A.s0[i] = 0.f;
+                A.s1[i] = 0.f;
+                A.s2[i] = 0.f;
+                A.sk[i] = 0.f;
+            }
             if constexpr (MODE == kJBF) {
                 A.c[i] = tcentre[i].x;
             } else if constexpr (MODE == kBF) {
@@ -291,8 +346,8 @@ __global__ void __launch_bounds__(kThreads, 2) stencil_kernel(const StencilArgs 
 #pragma unroll 1
         for (int ky = -radius; ky <= radius; ++ky) {
             const int hw = hw_s[ky + radius];
-            dispatch_row<MODE, P, RMAX, CLAMP>(hw, tcentre + ky * tp, ksw_s + (ky + radius) * (radius + 1), lutl, clamp_i,
-                                               clamp_f, A);
+            do_row<MODE, P, CLAMP>(2 * hw + 1, tcentre + ky * tp - hw, w_s + (ky + radius) * L.w_pitch, lut_addr, clamp_i,
+                                   clamp_f, A);
         }
 
         // epilogue: src/bilateral_filter_impl.cu:93-95
@@ -302,9 +357,16 @@ __global__ void __launch_bounds__(kThreads, 2) stencil_kernel(const StencilArgs 
             std::uint8_t o[3 * P];
 #pragma unroll
             for (int i = 0; i < P; ++i) {
-                o[3 * i + 0] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(A.s0[i], A.sk[i]), 0.5f));
-                o[3 * i + 1] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(A.s1[i], A.sk[i]), 0.5f));
-                o[3 * i + 2] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(A.s2[i], A.sk[i]), 0.5f));
+                float s0, s1, s2, sk;
+                if constexpr (UseFma2<MODE>::value) {
+                    unpack2(A.s01[i], s0, s1);
+                    unpack2(A.s2k[i], s2, sk);
+                } else {
+                    s0 = A.s0[i], s1 = A.s1[i], s2 = A.s2[i], sk = A.sk[i];
+                }
+                o[3 * i + 0] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(s0, sk), 0.5f));
+                o[3 * i + 1] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(s1, sk), 0.5f));
+                o[3 * i + 2] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(s2, sk), 0.5f));
             }
             std::uint8_t* const drow = a.dst + (static_cast<size_t>(y - a.dst_y0) * W + x0) * 3;
             if (x0 + P <= W && (reinterpret_cast<std::uintptr_t>(drow) & 3u) == 0) {
@@ -388,10 +450,10 @@ __global__ void stencil_generic_kernel(const StencilArgs a, const int lut_len) {
     d[2] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(s2, sk), 0.5f));
 }
 
-template <int MODE, int P, int RMAX, bool CLAMP>
+template <int MODE, int P, bool CLAMP>
 cudaError_t launch_tiled(const StencilArgs& a, int sm_count, cudaStream_t stream) {
     const SmemLayout L = make_layout(MODE, P, a.radius, a.lut_n);
-    auto kern = stencil_kernel<MODE, P, RMAX, CLAMP>;
+    auto kern = stencil_kernel<MODE, P, CLAMP>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total);
     if (e != cudaSuccess) return e;
     const int tiles_x = (a.width + kWarps * P - 1) / (kWarps * P);
@@ -406,13 +468,6 @@ cudaError_t launch_tiled(const StencilArgs& a, int sm_count, cudaStream_t stream
     kern<<<grid, kThreads, L.total, stream>>>(a, tiles_x, n_tiles);
     count_launch();
     return cudaGetLastError();
-}
-
-template <int MODE, int P, bool CLAMP>
-cudaError_t launch_by_radius(const StencilArgs& a, int sm_count, cudaStream_t stream) {
-    if (a.radius <= 5) return launch_tiled<MODE, P, 5, CLAMP>(a, sm_count, stream);
-    if (a.radius <= 8) return launch_tiled<MODE, P, 8, CLAMP>(a, sm_count, stream);
-    return launch_tiled<MODE, P, 15, CLAMP>(a, sm_count, stream);
 }
 
 template <int MODE>
@@ -452,14 +507,14 @@ cudaError_t launch_stencil(StencilMode mode, const StencilArgs& a, int sm_count,
     const bool clamp = a.lut_clamp != 0;
     switch (mode) {
         case kBF:
-            return clamp ? launch_by_radius<kBF, 8, true>(a, sm_count, stream)
-                         : launch_by_radius<kBF, 8, false>(a, sm_count, stream);
+            return clamp ? launch_tiled<kBF, 8, true>(a, sm_count, stream)
+                         : launch_tiled<kBF, 8, false>(a, sm_count, stream);
         case kJBF:
-            return clamp ? launch_by_radius<kJBF, 8, true>(a, sm_count, stream)
-                         : launch_by_radius<kJBF, 8, false>(a, sm_count, stream);
+            return clamp ? launch_tiled<kJBF, 8, true>(a, sm_count, stream)
+                         : launch_tiled<kJBF, 8, false>(a, sm_count, stream);
         default:
-            return clamp ? launch_by_radius<kABF, 8, true>(a, sm_count, stream)
-                         : launch_by_radius<kABF, 8, false>(a, sm_count, stream);
+            return clamp ? launch_tiled<kABF, 8, true>(a, sm_count, stream)
+                         : launch_tiled<kABF, 8, false>(a, sm_count, stream);
     }
 }
 
