@@ -1,24 +1,30 @@
 // Bilateral-texture-filter stage kernels for sm_100a.  Replace compute_blur_and_rtv_kernel
-// (src/bilateral_texture_filter_impl.cu:10-104) and compute_guide_kernel (:106-177).  New design:
+// (src/bilateral_texture_filter_impl.cu:10-104), compute_guide_kernel (:106-177) and -- fused into the first --
+// compute_gradient_kernel (src/gradient_impl.cu:7-77).  New design:
 //
-//  blur / mRTV   Everything that is order-independent is made separable and exact: the k x k box sums of the
-//                three channels and the min / max of (b+g+r) are integers (the reference's float running sums
-//                of u8 values are exact integers < 2^24, and (b+g+r)/3.f is monotone, so min/max commute with
-//                it); the max of the gradient magnitude is a float max.  A horizontal pass over the shared tile
-//                writes one 16-byte record per (row, column), a vertical pass folds k records per output.
-//                The SUM of the magnitudes is the one quantity whose fp32 rounding depends on the order, and the
-//                argmin in the next stage amplifies a 1-ulp difference into a different guide pixel
-//                (hard part 3), so it is accumulated in the reference's raster order (ky outer, kx
-//                inner), with each lane owning an image row and 4 adjacent outputs so that one shared load
-//                feeds up to 4 accumulators.  The final divide is done in fp64 like the reference
-//                (its epsilon is a double literal, :8, :103).
+//  blur / mRTV   One CTA (256 threads) produces a 64 x 32 tile; a lane owns a COLUMN (global loads/stores are
+//                coalesced, shared-memory rows are read conflict-free) and 8 consecutive rows.
+//                * the image tile (+ radius + 1 halo) is staged as packed 32-bit pixels; the gradient magnitude of
+//                  the tile (+ radius halo) is computed from it in shared memory (VABSDIFF4 + IDP4A: exact integers,
+//                  then the correctly rounded sqrtf), so the magnitude image never goes through HBM;
+//                * everything order-independent is made separable and exact: k x k box sums of the three channels
+//                  and min / max of (b+g+r) are integers (the reference's float running sums of u8 values are exact
+//                  integers < 2^24, and (b+g+r)/3.f is monotone, so min/max commute with it), the max of the
+//                  magnitude is a float max.  A horizontal pass writes one 16-byte record per (row, column), the
+//                  vertical pass folds k records per output while the records slide through registers;
+//                * the SUM of the magnitudes is the one quantity whose fp32 rounding depends on the order, and the
+//                  argmin of the next stage amplifies a 1-ulp difference into a different guide pixel
+//                  (hard part 3): it is accumulated in the reference's raster order (ky outer, kx
+//                  inner), one shared-memory row load feeding the chains of up to 8 outputs.  The final divide is
+//                  fp64 like the reference (its epsilon is a double literal, :8, :103).
 //  guide         The k x k argmin with "first in raster order wins" is separable as a lexicographic
-//                (value, ky, kx) minimum: a horizontal pass keeps the smallest kx among equal values, the
+//                (value, ky, kx) minimum: the horizontal pass keeps the smallest kx among equal values, the
 //                vertical pass the smallest ky.  alpha, the blend (fma(alpha, Bq, (1-alpha)*Bp) + 0.5f, the
-//                contraction nvcc applies to the reference), truncation and clamp follow :167-176.
+//                contraction nvcc applies to the reference), truncation and clamp follow :167-176.  The tile's
+//                output bytes are staged in shared memory and stored as coalesced 32-bit words.
 //
-// In both kernels a lane owns one image row (odd shared pitches make that bank-conflict free) and a warp
-// owns 4 columns x 32 rows; a 256-thread CTA produces 32 x 32 outputs.
+// Window sizes 3..15 run the tiled kernels (instantiated per k: the loops are fully unrolled); anything else runs
+// a plain one-thread-per-pixel kernel with the same arithmetic.
 #include <cuda_runtime.h>
 
 #include <cstdint>
@@ -29,8 +35,9 @@ namespace vip {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kTile = 32;
-constexpr int kP = 4;
+constexpr int kTW = 64;    // tile columns: 2 warps side by side
+constexpr int kTH = 32;    // tile rows:    4 warp rows x 8 rows per thread
+constexpr int kRows = 8;   // consecutive output rows per thread
 
 __device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
@@ -39,327 +46,461 @@ __device__ __forceinline__ std::uint32_t load_packed(const std::uint8_t* __restr
            (static_cast<std::uint32_t>(__ldg(p + 2)) << 16);
 }
 
-struct BlurLayout {
-    int tw, th, tp, hp, pix_off, mag_off, hs_off, total;
-};
-__host__ __device__ inline BlurLayout blur_layout(int k) {
-    BlurLayout L;
-    L.tw = kTile + k - 1;
-    L.th = kTile + k - 1;
-    L.tp = L.tw | 1;
-    L.hp = kTile + 1;
-    L.pix_off = 0;
-    L.mag_off = L.tp * L.th * 4;
-    L.hs_off = (2 * L.tp * L.th * 4 + 15) & ~15;
-    L.total = L.hs_off + L.hp * L.th * 16;
-    return L;
+// sum over the three colour bytes of (a_c - b_c)^2, exact
+__device__ __forceinline__ int sq_diff(const std::uint32_t a, const std::uint32_t b) {
+    const std::uint32_t d = __vabsdiffu4(a, b);
+    return __dp4a(d, d, 0u);
 }
 
-// KT > 0: compile-time window size (unrolled, no predication); KT == 0: runtime k.
-template <int KT>
-__global__ void __launch_bounds__(kThreads) blur_rtv_kernel(const std::uint8_t* __restrict__ image,
-                                                           const float* __restrict__ magnitude,
-                                                           float* __restrict__ blurred, float* __restrict__ rtv,
-                                                           const int W, const int H, const int k_rt, const int src_y0,
-                                                           const int dst_y0, const int out_y0, const int out_rows) {
+template <int K>
+struct BlurLayout {
+    static constexpr int r = K / 2;
+    static constexpr int PW = kTW + 2 * r + 2, PH = kTH + 2 * r + 2;  // packed pixels, radius + 1 halo
+    static constexpr int MW = kTW + 2 * r, MH = kTH + 2 * r;          // magnitudes / records, radius halo
+    static constexpr int pix_off = 0;
+    static constexpr int mag_off = (PW * PH * 4 + 15) & ~15;
+    static constexpr int hs_off = (mag_off + MW * MH * 4 + 15) & ~15;
+    static constexpr int total = hs_off + MH * kTW * 16;
+};
+
+struct RowMap {
+    int H, src_y0, src_rows;
+    // buffer row of full-image row y (clamped to the image, then -- for rows no valid output depends on -- to the strip)
+    __device__ __forceinline__ int operator()(int y) const {
+        return clampi(clampi(y, 0, H - 1), src_y0, src_y0 + src_rows - 1) - src_y0;
+    }
+};
+
+// FUSED: magnitude == nullptr, the gradient magnitude is computed from the image tile.
+template <int K, bool FUSED>
+__global__ void __launch_bounds__(kThreads, 3) blur_rtv_kernel(const std::uint8_t* __restrict__ image,
+                                                              const float* __restrict__ magnitude,
+                                                              float* __restrict__ blurred, float* __restrict__ rtv,
+                                                              const int W, const int H, const int src_y0,
+                                                              const int src_rows, const int dst_y0, const int out_y0,
+                                                              const int out_rows) {
+    using L = BlurLayout<K>;
+    constexpr int r = L::r;
     extern __shared__ __align__(16) unsigned char smem[];
-    const int k = KT > 0 ? KT : k_rt;
-    const int r = k / 2;
-    const BlurLayout L = blur_layout(k);
-    std::uint32_t* const pix = reinterpret_cast<std::uint32_t*>(smem + L.pix_off);
-    float* const mag = reinterpret_cast<float*>(smem + L.mag_off);
-    uint4* const hs = reinterpret_cast<uint4*>(smem + L.hs_off);
+    std::uint32_t* const pix = reinterpret_cast<std::uint32_t*>(smem + L::pix_off);
+    float* const mag = reinterpret_cast<float*>(smem + L::mag_off);
+    uint4* const hs = reinterpret_cast<uint4*>(smem + L::hs_off);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int X0 = blockIdx.x * kTile;
-    const int Y0 = out_y0 + blockIdx.y * kTile;
+    const int X0 = blockIdx.x * kTW;
+    const int Y0 = out_y0 + blockIdx.y * kTH;
+    const RowMap rowmap{H, src_y0, src_rows};
 
-    for (int e = tid; e < L.tw * L.th; e += kThreads) {
-        const int ey = e / L.tw, ex = e - ey * L.tw;
-        const int gx = clampi(X0 - r + ex, 0, W - 1);
-        const int gy = clampi(Y0 - r + ey, 0, H - 1) - src_y0;
-        const size_t o = static_cast<size_t>(gy) * W + gx;
-        pix[ey * L.tp + ex] = load_packed(image + o * 3);
-        mag[ey * L.tp + ex] = __ldg(magnitude + o);
+    // A. packed pixels of [X0-r-1, X0+kTW+r+1) x [Y0-r-1, Y0+kTH+r+1), coordinates clamped to the image
+    for (int e = tid; e < L::PW * L::PH; e += kThreads) {
+        const int ey = e / L::PW, ex = e - ey * L::PW;
+        const int gx = clampi(X0 - r - 1 + ex, 0, W - 1);
+        const int gy = rowmap(Y0 - r - 1 + ey);
+        pix[e] = load_packed(image + (static_cast<size_t>(gy) * W + gx) * 3);
+    }
+    if constexpr (!FUSED) {
+        for (int e = tid; e < L::MW * L::MH; e += kThreads) {
+            const int my = e / L::MW, mx = e - my * L::MW;
+            const int gx = clampi(X0 - r + mx, 0, W - 1);
+            const int gy = rowmap(Y0 - r + my);
+            mag[e] = __ldg(magnitude + static_cast<size_t>(gy) * W + gx);
+        }
     }
     __syncthreads();
 
-    // horizontal pass: record = {B | R<<16, G, min(b+g+r) | max(b+g+r)<<16, max magnitude} over k columns
-    for (int e = tid; e < L.th * kTile; e += kThreads) {
-        const int row = e / kTile, col = e - row * kTile;
-        const std::uint32_t* pr = pix + row * L.tp + col;
-        const float* mr = mag + row * L.tp + col;
+    // B. gradient magnitude at the CLAMPED coordinate of every tile position (src/gradient_impl.cu:52-65):
+    //    central differences with clamped neighbours, integer squares, sqrtf
+    if constexpr (FUSED) {
+        for (int e = tid; e < L::MW * L::MH; e += kThreads) {
+            const int my = e / L::MW, mx = e - my * L::MW;
+            const int cx = clampi(X0 - r + mx, 0, W - 1), cy = clampi(Y0 - r + my, 0, H - 1);
+            const int tx = cx - (X0 - r - 1), ty = cy - (Y0 - r - 1);
+            const std::uint32_t* c = pix + ty * L::PW + tx;
+            const int xm = cx > 0 ? -1 : 0, xp = cx < W - 1 ? 1 : 0;
+            const int ym = cy > 0 ? -L::PW : 0, yp = cy < H - 1 ? L::PW : 0;
+            const int acc = sq_diff(c[xp], c[xm]) + sq_diff(c[yp], c[ym]);
+            mag[e] = sqrtf(static_cast<float>(acc));
+        }
+        __syncthreads();
+    }
+
+    // C. horizontal pass: record = {B | R<<16, G, min(b+g+r) | max(b+g+r)<<16, max magnitude} over K columns
+    for (int e = tid; e < L::MH * kTW; e += kThreads) {
+        const int row = e / kTW, col = e - row * kTW;
+        const std::uint32_t* pr = pix + (row + 1) * L::PW + col + 1;
+        const float* mr = mag + row * L::MW + col;
         std::uint32_t br = 0, g = 0, mn = 0xffffu, mx = 0;
         float mm = 0.f;
 #pragma unroll
-        for (int j = 0; j < (KT > 0 ? KT : 1); ++j) {
-            if (KT == 0) break;
+        for (int j = 0; j < K; ++j) {
             const std::uint32_t p = pr[j];
             const std::uint32_t s = __vsadu4(p, 0u);
-            br += p & 0x00ff00ffu;
-            g += (p >> 8) & 0xffu;
+            br += __byte_perm(p, 0u, 0x4240);
+            g += __byte_perm(p, 0u, 0x4441);
             mn = min(mn, s);
             mx = max(mx, s);
             mm = fmaxf(mm, mr[j]);
         }
-        if (KT == 0) {
-            for (int j = 0; j < k; ++j) {
-                const std::uint32_t p = pr[j];
-                const std::uint32_t s = __vsadu4(p, 0u);
-                br += p & 0x00ff00ffu;
-                g += (p >> 8) & 0xffu;
-                mn = min(mn, s);
-                mx = max(mx, s);
-                mm = fmaxf(mm, mr[j]);
-            }
-        }
-        hs[row * L.hp + col] = make_uint4(br, g, mn | (mx << 16), __float_as_uint(mm));
+        hs[e] = make_uint4(br, g, mn | (mx << 16), __float_as_uint(mm));
     }
     __syncthreads();
 
-    // vertical pass + raster-order magnitude sum; lane <-> row, 4 adjacent outputs per thread
-    const int xl = warp * kP;
-    std::uint32_t sb[kP], sg[kP], sr[kP], mn[kP], mx[kP];
-    float mm[kP], msum[kP];
+    // D. vertical pass + raster-order magnitude sum; lane <-> column, kRows consecutive rows per thread
+    const int col = (warp & 1) * 32 + lane;
+    const int r0 = (warp >> 1) * kRows;
+    std::uint32_t sbr[kRows], sg[kRows], mn[kRows], mx[kRows];
+    float mm[kRows], msum[kRows];
 #pragma unroll
-    for (int i = 0; i < kP; ++i) {
-        sb[i] = sg[i] = sr[i] = 0;
+    for (int i = 0; i < kRows; ++i) {
+        sbr[i] = sg[i] = 0;
         mn[i] = 0xffffu;
         mx[i] = 0;
         mm[i] = 0.f;
         msum[i] = 0.f;
     }
-    if (KT > 0) {
 #pragma unroll
-        for (int ky = 0; ky < (KT > 0 ? KT : 1); ++ky) {
-            const uint4* hrow = hs + (lane + ky) * L.hp + xl;
+    for (int R = 0; R < K + kRows - 1; ++R) {
+        const uint4 h = hs[(r0 + R) * kTW + col];
+        float v[K];
 #pragma unroll
-            for (int i = 0; i < kP; ++i) {
-                const uint4 h = hrow[i];
-                sb[i] += h.x & 0xffffu;
-                sr[i] += h.x >> 16;
+        for (int j = 0; j < K; ++j) v[j] = mag[(r0 + R) * L::MW + col + j];
+#pragma unroll
+        for (int i = 0; i < kRows; ++i) {
+            if (R - i >= 0 && R - i < K) {
+                sbr[i] += h.x;
                 sg[i] += h.y;
                 mn[i] = min(mn[i], h.z & 0xffffu);
                 mx[i] = max(mx[i], h.z >> 16);
                 mm[i] = fmaxf(mm[i], __uint_as_float(h.w));
-            }
-            const float* mrow = mag + (lane + ky) * L.tp + xl;
 #pragma unroll
-            for (int j = 0; j < (KT > 0 ? KT : 1) + kP - 1; ++j) {
-                const float v = mrow[j];
-#pragma unroll
-                for (int i = 0; i < kP; ++i) {
-                    if (j - i >= 0 && j - i < KT) msum[i] = __fadd_rn(msum[i], v);
-                }
-            }
-        }
-    } else {
-        for (int ky = 0; ky < k; ++ky) {
-            const uint4* hrow = hs + (lane + ky) * L.hp + xl;
-#pragma unroll
-            for (int i = 0; i < kP; ++i) {
-                const uint4 h = hrow[i];
-                sb[i] += h.x & 0xffffu;
-                sr[i] += h.x >> 16;
-                sg[i] += h.y;
-                mn[i] = min(mn[i], h.z & 0xffffu);
-                mx[i] = max(mx[i], h.z >> 16);
-                mm[i] = fmaxf(mm[i], __uint_as_float(h.w));
-            }
-            const float* mrow = mag + (lane + ky) * L.tp + xl;
-            for (int j = 0; j < k + kP - 1; ++j) {
-                const float v = mrow[j];
-#pragma unroll
-                for (int i = 0; i < kP; ++i) {
-                    if (j - i >= 0 && j - i < k) msum[i] = __fadd_rn(msum[i], v);
-                }
+                for (int j = 0; j < K; ++j) msum[i] = __fadd_rn(msum[i], v[j]);
             }
         }
     }
 
-    const int y = Y0 + lane;
-    const int x0 = X0 + xl;
-    if (y >= out_y0 + out_rows || x0 >= W) return;
-    const float kk = static_cast<float>(k * k);
-    float bl[3 * kP], rt[kP];
+    // E. epilogue (:88-103) and coalesced stores
+    const int x = X0 + col;
+    if (x >= W) return;
+    const float kk = static_cast<float>(K * K);
 #pragma unroll
-    for (int i = 0; i < kP; ++i) {
-        bl[3 * i + 0] = __fdiv_rn(static_cast<float>(sb[i]), kk);
-        bl[3 * i + 1] = __fdiv_rn(static_cast<float>(sg[i]), kk);
-        bl[3 * i + 2] = __fdiv_rn(static_cast<float>(sr[i]), kk);
+    for (int i = 0; i < kRows; ++i) {
+        const int y = Y0 + r0 + i;
+        if (y >= out_y0 + out_rows) break;
+        const size_t o = static_cast<size_t>(y - dst_y0) * W + x;
+        blurred[o * 3 + 0] = __fdiv_rn(static_cast<float>(sbr[i] & 0xffffu), kk);
+        blurred[o * 3 + 1] = __fdiv_rn(static_cast<float>(sg[i]), kk);
+        blurred[o * 3 + 2] = __fdiv_rn(static_cast<float>(sbr[i] >> 16), kk);
         const float imax = __fdiv_rn(static_cast<float>(mx[i]), 3.f);
         const float imin = __fdiv_rn(static_cast<float>(mn[i]), 3.f);
         const float num = __fmul_rn(__fsub_rn(imax, imin), mm[i]);
-        rt[i] = static_cast<float>(static_cast<double>(num) / (static_cast<double>(msum[i]) + 1e-9));
+        rtv[o] = static_cast<float>(static_cast<double>(num) / (static_cast<double>(msum[i]) + 1e-9));
     }
-    const size_t o = static_cast<size_t>(y - dst_y0) * W + x0;
-    float* bp = blurred + o * 3;
-    float* rp = rtv + o;
-    if (x0 + kP <= W && ((reinterpret_cast<std::uintptr_t>(bp) | reinterpret_cast<std::uintptr_t>(rp)) & 15u) == 0) {
-        reinterpret_cast<float4*>(bp)[0] = make_float4(bl[0], bl[1], bl[2], bl[3]);
-        reinterpret_cast<float4*>(bp)[1] = make_float4(bl[4], bl[5], bl[6], bl[7]);
-        reinterpret_cast<float4*>(bp)[2] = make_float4(bl[8], bl[9], bl[10], bl[11]);
-        *reinterpret_cast<float4*>(rp) = make_float4(rt[0], rt[1], rt[2], rt[3]);
-    } else {
-#pragma unroll
-        for (int i = 0; i < kP; ++i) {
-            if (x0 + i < W) {
-                bp[3 * i + 0] = bl[3 * i + 0];
-                bp[3 * i + 1] = bl[3 * i + 1];
-                bp[3 * i + 2] = bl[3 * i + 2];
-                rp[i] = rt[i];
+}
+
+// Any window size: one thread per pixel straight from global memory, same arithmetic.
+__global__ void blur_rtv_generic_kernel(const std::uint8_t* __restrict__ image, const float* __restrict__ magnitude,
+                                        float* __restrict__ blurred, float* __restrict__ rtv, const int W, const int H,
+                                        const int k, const int src_y0, const int src_rows, const int dst_y0,
+                                        const int out_y0, const int out_rows) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = out_y0 + blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= W || y >= out_y0 + out_rows) return;
+    const RowMap rowmap{H, src_y0, src_rows};
+    const int r = k / 2;
+    int s0 = 0, s1 = 0, s2 = 0, mn = 0xffff, mx = 0;
+    float mm = 0.f, msum = 0.f;
+    for (int ky = -r; ky <= r; ++ky) {
+        const int cy = clampi(y + ky, 0, H - 1);
+        const int yy = rowmap(cy);
+        for (int kx = -r; kx <= r; ++kx) {
+            const int cx = clampi(x + kx, 0, W - 1);
+            const std::uint8_t* p = image + (static_cast<size_t>(yy) * W + cx) * 3;
+            const int b = p[0], g = p[1], rr = p[2];
+            s0 += b;
+            s1 += g;
+            s2 += rr;
+            mn = min(mn, b + g + rr);
+            mx = max(mx, b + g + rr);
+            float m;
+            if (magnitude) {
+                m = __ldg(magnitude + static_cast<size_t>(yy) * W + cx);
+            } else {
+                const int xm = max(cx - 1, 0), xp = min(cx + 1, W - 1);
+                const std::uint8_t* pu = image + (static_cast<size_t>(rowmap(cy - 1)) * W + cx) * 3;
+                const std::uint8_t* pd = image + (static_cast<size_t>(rowmap(cy + 1)) * W + cx) * 3;
+                const std::uint8_t* pl = image + (static_cast<size_t>(yy) * W + xm) * 3;
+                const std::uint8_t* pr = image + (static_cast<size_t>(yy) * W + xp) * 3;
+                int acc = 0;
+                for (int c = 0; c < 3; ++c) {
+                    const int dx = static_cast<int>(pr[c]) - static_cast<int>(pl[c]);
+                    const int dy = static_cast<int>(pd[c]) - static_cast<int>(pu[c]);
+                    acc += dx * dx + dy * dy;
+                }
+                m = sqrtf(static_cast<float>(acc));
             }
+            mm = fmaxf(mm, m);
+            msum = __fadd_rn(msum, m);
         }
     }
+    const float kk = static_cast<float>(k * k);
+    const size_t o = static_cast<size_t>(y - dst_y0) * W + x;
+    blurred[o * 3 + 0] = __fdiv_rn(static_cast<float>(s0), kk);
+    blurred[o * 3 + 1] = __fdiv_rn(static_cast<float>(s1), kk);
+    blurred[o * 3 + 2] = __fdiv_rn(static_cast<float>(s2), kk);
+    const float imax = __fdiv_rn(static_cast<float>(mx), 3.f);
+    const float imin = __fdiv_rn(static_cast<float>(mn), 3.f);
+    const float num = __fmul_rn(__fsub_rn(imax, imin), mm);
+    rtv[o] = static_cast<float>(static_cast<double>(num) / (static_cast<double>(msum) + 1e-9));
 }
 
+template <int K>
 struct GuideLayout {
-    int tw, th, tp, hp, hs_off, total;
+    static constexpr int r = K / 2;
+    static constexpr int MW = kTW + 2 * r, MH = kTH + 2 * r;
+    static constexpr int hs_off = (MW * MH * 4 + 15) & ~15;
+    static constexpr int out_off = hs_off + MH * kTW * 8;
+    static constexpr int total = out_off + kTH * kTW * 3;
 };
-__host__ __device__ inline GuideLayout guide_layout(int k) {
-    GuideLayout L;
-    L.tw = kTile + k - 1;
-    L.th = kTile + k - 1;
-    L.tp = L.tw | 1;
-    L.hp = kTile + 1;
-    L.hs_off = (L.tp * L.th * 4 + 15) & ~15;
-    L.total = L.hs_off + L.hp * L.th * 8;
-    return L;
+
+// alpha and the blend of one guide pixel (:167-176); bq / bp point at the 3 blurred floats of the argmin / centre pixel
+__device__ __forceinline__ void guide_pixel(const float rtv_p, const float rtv_min, const float sigma_alpha,
+                                            const float* __restrict__ bq, const float* __restrict__ bp,
+                                            std::uint8_t* out) {
+    const float e = expf(__fmul_rn(sigma_alpha, __fsub_rn(rtv_p, rtv_min)));
+    const float alpha = __fsub_rn(__fdiv_rn(2.f, __fadd_rn(1.f, e)), 1.f);
+    const float one_m = __fsub_rn(1.f, alpha);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float t = __fadd_rn(__fmaf_rn(alpha, __ldg(bq + c), __fmul_rn(one_m, __ldg(bp + c))), 0.5f);
+        out[c] = static_cast<std::uint8_t>(clampi(__float2int_rz(t), 0, 255));
+    }
 }
 
-__global__ void __launch_bounds__(kThreads) guide_kernel(const float* __restrict__ blurred,
-                                                        const float* __restrict__ rtv, std::uint8_t* __restrict__ guide,
-                                                        const int W, const int H, const int k, const int src_y0,
-                                                        const int dst_y0, const int out_y0, const int out_rows) {
+template <int K>
+__global__ void __launch_bounds__(kThreads, 4) guide_kernel(const float* __restrict__ blurred,
+                                                           const float* __restrict__ rtv, std::uint8_t* __restrict__ guide,
+                                                           const int W, const int H, const int src_y0, const int src_rows,
+                                                           const int dst_y0, const int out_y0, const int out_rows) {
+    using L = GuideLayout<K>;
+    constexpr int r = L::r;
     extern __shared__ __align__(16) unsigned char smem[];
-    const int r = k / 2;
-    const GuideLayout L = guide_layout(k);
     float* const tile = reinterpret_cast<float*>(smem);
-    float2* const hs = reinterpret_cast<float2*>(smem + L.hs_off);
+    float2* const hs = reinterpret_cast<float2*>(smem + L::hs_off);
+    std::uint8_t* const obuf = smem + L::out_off;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int X0 = blockIdx.x * kTile;
-    const int Y0 = out_y0 + blockIdx.y * kTile;
+    const int X0 = blockIdx.x * kTW;
+    const int Y0 = out_y0 + blockIdx.y * kTH;
+    const RowMap rowmap{H, src_y0, src_rows};
 
-    for (int e = tid; e < L.tw * L.th; e += kThreads) {
-        const int ey = e / L.tw, ex = e - ey * L.tw;
+    for (int e = tid; e < L::MW * L::MH; e += kThreads) {
+        const int ey = e / L::MW, ex = e - ey * L::MW;
         const int gx = clampi(X0 - r + ex, 0, W - 1);
-        const int gy = clampi(Y0 - r + ey, 0, H - 1) - src_y0;
-        tile[ey * L.tp + ex] = __ldg(rtv + static_cast<size_t>(gy) * W + gx);
+        tile[e] = __ldg(rtv + static_cast<size_t>(rowmap(Y0 - r + ey)) * W + gx);
     }
     __syncthreads();
 
-    // horizontal pass: (min value, smallest kx attaining it); strict '<' keeps the first
-    for (int e = tid; e < L.th * kTile; e += kThreads) {
-        const int row = e / kTile, col = e - row * kTile;
-        const float* tr = tile + row * L.tp + col;
-        float best = 1e10f;  // src/bilateral_texture_filter_impl.cu:152
+    // horizontal pass: (min value, smallest kx attaining it); strict '>' keeps the first (:152-165)
+    for (int e = tid; e < L::MH * kTW; e += kThreads) {
+        const int row = e / kTW, col = e - row * kTW;
+        const float* tr = tile + row * L::MW + col;
+        float best = 1e10f;  // :152
         int bj = -1;
-        for (int j = 0; j < k; ++j) {
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
             const float v = tr[j];
             if (best > v) {
                 best = v;
                 bj = j;
             }
         }
-        hs[row * L.hp + col] = make_float2(best, __int_as_float(bj));
+        hs[e] = make_float2(best, __int_as_float(bj));
     }
     __syncthreads();
 
-    const int xl = warp * kP;
-    const int y = Y0 + lane;
-    const int x0 = X0 + xl;
-    if (y >= out_y0 + out_rows || x0 >= W) return;
-    const float sigma_alpha = __fdiv_rn(1.f, static_cast<float>(5 * k));  // :121
-    std::uint8_t out[3 * kP];
+    const int col = (warp & 1) * 32 + lane;
+    const int r0 = (warp >> 1) * kRows;
+    const int x = min(X0 + col, W - 1);
+    const float sigma_alpha = __fdiv_rn(1.f, static_cast<float>(5 * K));  // :121
+    float best[kRows];
+    int bj[kRows], bky[kRows];
 #pragma unroll
-    for (int i = 0; i < kP; ++i) {
-        float best = 1e10f;
-        int bj = -1, bky = 0;
-        const float2* hcol = hs + lane * L.hp + xl + i;
-        for (int ky = 0; ky < k; ++ky) {
-            const float2 h = hcol[ky * L.hp];
-            if (best > h.x) {
-                best = h.x;
-                bj = __float_as_int(h.y);
-                bky = ky;
+    for (int i = 0; i < kRows; ++i) {
+        best[i] = 1e10f;
+        bj[i] = -1;
+        bky[i] = 0;
+    }
+#pragma unroll
+    for (int R = 0; R < K + kRows - 1; ++R) {
+        const float2 h = hs[(r0 + R) * kTW + col];
+#pragma unroll
+        for (int i = 0; i < kRows; ++i) {
+            if (R - i >= 0 && R - i < K) {
+                if (best[i] > h.x) {
+                    best[i] = h.x;
+                    bj[i] = __float_as_int(h.y);
+                    bky[i] = R - i;
+                }
             }
-        }
-        const int x = min(x0 + i, W - 1);
-        int mx = 0, my = 0;  // the reference's initial coordinates when nothing is below 1e10f
-        if (bj >= 0) {
-            mx = clampi(x + bj - r, 0, W - 1);
-            my = clampi(y + bky - r, 0, H - 1);
-        } else {
-            best = __ldg(rtv + static_cast<size_t>(clampi(0, 0, H - 1) - src_y0) * W);
-        }
-        const float rp = tile[(lane + r) * L.tp + xl + i + r];
-        const float e = expf(__fmul_rn(sigma_alpha, __fsub_rn(rp, best)));
-        const float alpha = __fsub_rn(__fdiv_rn(2.f, __fadd_rn(1.f, e)), 1.f);  // :167
-        const float one_m = __fsub_rn(1.f, alpha);
-        const float* bq = blurred + (static_cast<size_t>(my - src_y0) * W + mx) * 3;
-        const float* bp = blurred + (static_cast<size_t>(y - src_y0) * W + x) * 3;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            const float t = __fadd_rn(__fmaf_rn(alpha, __ldg(bq + c), __fmul_rn(one_m, __ldg(bp + c))), 0.5f);
-            out[3 * i + c] = static_cast<std::uint8_t>(clampi(__float2int_rz(t), 0, 255));
         }
     }
-    std::uint8_t* gp = guide + (static_cast<size_t>(y - dst_y0) * W + x0) * 3;
-    if (x0 + kP <= W && (reinterpret_cast<std::uintptr_t>(gp) & 3u) == 0) {
 #pragma unroll
-        for (int j = 0; j < 3; ++j) {
-            reinterpret_cast<std::uint32_t*>(gp)[j] = out[4 * j] | (out[4 * j + 1] << 8) | (out[4 * j + 2] << 16) |
-                                                       (static_cast<std::uint32_t>(out[4 * j + 3]) << 24);
+    for (int i = 0; i < kRows; ++i) {
+        const int y = min(Y0 + r0 + i, H - 1);
+        int mx = 0, my = 0;  // the reference's initial coordinates when nothing is below 1e10f
+        float rmin = best[i];
+        if (bj[i] >= 0) {
+            mx = clampi(x + bj[i] - r, 0, W - 1);
+            my = clampi(y + bky[i] - r, 0, H - 1);
+        } else {
+            rmin = __ldg(rtv + static_cast<size_t>(rowmap(0)) * W);
         }
-    } else {
-#pragma unroll
-        for (int i = 0; i < kP; ++i) {
-            if (x0 + i < W) {
-                gp[3 * i + 0] = out[3 * i + 0];
-                gp[3 * i + 1] = out[3 * i + 1];
-                gp[3 * i + 2] = out[3 * i + 2];
-            }
+        const float rp = tile[(r0 + i + r) * L::MW + col + r];
+        const float* bq = blurred + (static_cast<size_t>(rowmap(my)) * W + mx) * 3;
+        const float* bp = blurred + (static_cast<size_t>(rowmap(y)) * W + x) * 3;
+        guide_pixel(rp, rmin, sigma_alpha, bq, bp, obuf + ((r0 + i) * kTW + col) * 3);
+    }
+    __syncthreads();
+
+    // store the tile: rows of up to 192 bytes, as 32-bit words when the row start is aligned
+    const int cols = min(kTW, W - X0);
+    const int rows = min(kTH, out_y0 + out_rows - Y0);
+    const int row_bytes = cols * 3;
+    for (int row = warp; row < rows; row += kThreads / 32) {
+        std::uint8_t* g = guide + (static_cast<size_t>(Y0 + row - dst_y0) * W + X0) * 3;
+        const std::uint8_t* s = obuf + row * kTW * 3;
+        if ((reinterpret_cast<std::uintptr_t>(g) & 3u) == 0) {
+            const int words = row_bytes >> 2;
+            for (int i = lane; i < words; i += 32)
+                reinterpret_cast<std::uint32_t*>(g)[i] = reinterpret_cast<const std::uint32_t*>(s)[i];
+            for (int i = (words << 2) + lane; i < row_bytes; i += 32) g[i] = s[i];
+        } else {
+            for (int i = lane; i < row_bytes; i += 32) g[i] = s[i];
         }
     }
 }
 
+__global__ void guide_generic_kernel(const float* __restrict__ blurred, const float* __restrict__ rtv,
+                                     std::uint8_t* __restrict__ guide, const int W, const int H, const int k,
+                                     const int src_y0, const int src_rows, const int dst_y0, const int out_y0,
+                                     const int out_rows) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = out_y0 + blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= W || y >= out_y0 + out_rows) return;
+    const RowMap rowmap{H, src_y0, src_rows};
+    const int r = k / 2;
+    float rmin = 1e10f;
+    int mx = 0, my = 0;
+    for (int ky = -r; ky <= r; ++ky) {
+        const int cy = clampi(y + ky, 0, H - 1);
+        for (int kx = -r; kx <= r; ++kx) {
+            const int cx = clampi(x + kx, 0, W - 1);
+            const float v = __ldg(rtv + static_cast<size_t>(rowmap(cy)) * W + cx);
+            if (rmin > v) {
+                rmin = v;
+                mx = cx;
+                my = cy;
+            }
+        }
+    }
+    const float rq = __ldg(rtv + static_cast<size_t>(rowmap(my)) * W + mx);
+    const float rp = __ldg(rtv + static_cast<size_t>(rowmap(y)) * W + x);
+    std::uint8_t out[3];
+    guide_pixel(rp, rq, __fdiv_rn(1.f, static_cast<float>(5 * k)),
+                blurred + (static_cast<size_t>(rowmap(my)) * W + mx) * 3,
+                blurred + (static_cast<size_t>(rowmap(y)) * W + x) * 3, out);
+    std::uint8_t* g = guide + (static_cast<size_t>(y - dst_y0) * W + x) * 3;
+    g[0] = out[0];
+    g[1] = out[1];
+    g[2] = out[2];
+}
+
+template <int K>
+cudaError_t launch_blur_rtv_k(const std::uint8_t* image, const float* magnitude, float* blurred, float* rtv, int W, int H,
+                              int src_y0, int src_rows, int dst_y0, int out_y0, int out_rows, cudaStream_t stream) {
+    using L = BlurLayout<K>;
+    const dim3 grid((W + kTW - 1) / kTW, (out_rows + kTH - 1) / kTH);
+    cudaError_t e;
+    if (magnitude) {
+        e = cudaFuncSetAttribute(blur_rtv_kernel<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::total);
+        if (e != cudaSuccess) return e;
+        blur_rtv_kernel<K, false><<<grid, kThreads, L::total, stream>>>(image, magnitude, blurred, rtv, W, H, src_y0,
+                                                                       src_rows, dst_y0, out_y0, out_rows);
+    } else {
+        e = cudaFuncSetAttribute(blur_rtv_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::total);
+        if (e != cudaSuccess) return e;
+        blur_rtv_kernel<K, true><<<grid, kThreads, L::total, stream>>>(image, nullptr, blurred, rtv, W, H, src_y0,
+                                                                      src_rows, dst_y0, out_y0, out_rows);
+    }
+    return cudaGetLastError();
+}
+
+template <int K>
+cudaError_t launch_guide_k(const float* blurred, const float* rtv, std::uint8_t* guide, int W, int H, int src_y0,
+                           int src_rows, int dst_y0, int out_y0, int out_rows, cudaStream_t stream) {
+    using L = GuideLayout<K>;
+    const dim3 grid((W + kTW - 1) / kTW, (out_rows + kTH - 1) / kTH);
+    cudaError_t e = cudaFuncSetAttribute(guide_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::total);
+    if (e != cudaSuccess) return e;
+    guide_kernel<K><<<grid, kThreads, L::total, stream>>>(blurred, rtv, guide, W, H, src_y0, src_rows, dst_y0, out_y0,
+                                                         out_rows);
+    return cudaGetLastError();
+}
+
 }  // namespace
 
+// magnitude == nullptr: the gradient magnitude of `image` is computed on the fly (fused gradient stage).
 cudaError_t launch_blur_rtv(const std::uint8_t* image, const float* magnitude, float* blurred, float* rtv, int width,
                             int height, int ksize, int src_y0, int src_rows, int dst_y0, int out_y0, int out_rows,
                             cudaStream_t stream) {
-    (void)src_rows;
     if (out_rows <= 0 || width <= 0) return cudaSuccess;
-    const BlurLayout L = blur_layout(ksize);
-    const dim3 grid((width + kTile - 1) / kTile, (out_rows + kTile - 1) / kTile);
-    cudaError_t e;
-    if (ksize == 9) {
-        e = cudaFuncSetAttribute(blur_rtv_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total);
-        if (e != cudaSuccess) return e;
-        blur_rtv_kernel<9><<<grid, kThreads, L.total, stream>>>(image, magnitude, blurred, rtv, width, height, ksize,
-                                                               src_y0, dst_y0, out_y0, out_rows);
-    } else {
-        e = cudaFuncSetAttribute(blur_rtv_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total);
-        if (e != cudaSuccess) return e;
-        blur_rtv_kernel<0><<<grid, kThreads, L.total, stream>>>(image, magnitude, blurred, rtv, width, height, ksize,
-                                                               src_y0, dst_y0, out_y0, out_rows);
-    }
     count_launch();
+#define VIP_BLUR_CASE(K)                                                                                         \
+    case K:                                                                                                      \
+        return launch_blur_rtv_k<K>(image, magnitude, blurred, rtv, width, height, src_y0, src_rows, dst_y0, out_y0, \
+                                    out_rows, stream);
+    switch (ksize) {
+        VIP_BLUR_CASE(3)
+        VIP_BLUR_CASE(5)
+        VIP_BLUR_CASE(7)
+        VIP_BLUR_CASE(9)
+        VIP_BLUR_CASE(11)
+        VIP_BLUR_CASE(13)
+        VIP_BLUR_CASE(15)
+        default:
+            break;
+    }
+#undef VIP_BLUR_CASE
+    const dim3 block(32, 8);
+    const dim3 grid((width + 31) / 32, (out_rows + 7) / 8);
+    blur_rtv_generic_kernel<<<grid, block, 0, stream>>>(image, magnitude, blurred, rtv, width, height, ksize, src_y0,
+                                                       src_rows, dst_y0, out_y0, out_rows);
     return cudaGetLastError();
 }
 
 cudaError_t launch_guide(const float* blurred, const float* rtv, std::uint8_t* guide, int width, int height, int ksize,
                          int src_y0, int src_rows, int dst_y0, int out_y0, int out_rows, cudaStream_t stream) {
-    (void)src_rows;
     if (out_rows <= 0 || width <= 0) return cudaSuccess;
-    const GuideLayout L = guide_layout(ksize);
-    const dim3 grid((width + kTile - 1) / kTile, (out_rows + kTile - 1) / kTile);
-    cudaError_t e = cudaFuncSetAttribute(guide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total);
-    if (e != cudaSuccess) return e;
-    guide_kernel<<<grid, kThreads, L.total, stream>>>(blurred, rtv, guide, width, height, ksize, src_y0, dst_y0, out_y0,
-                                                     out_rows);
     count_launch();
+#define VIP_GUIDE_CASE(K)                                                                                            \
+    case K:                                                                                                          \
+        return launch_guide_k<K>(blurred, rtv, guide, width, height, src_y0, src_rows, dst_y0, out_y0, out_rows, stream);
+    switch (ksize) {
+        VIP_GUIDE_CASE(3)
+        VIP_GUIDE_CASE(5)
+        VIP_GUIDE_CASE(7)
+        VIP_GUIDE_CASE(9)
+        VIP_GUIDE_CASE(11)
+        VIP_GUIDE_CASE(13)
+        VIP_GUIDE_CASE(15)
+        default:
+            break;
+    }
+#undef VIP_GUIDE_CASE
+    const dim3 block(32, 8);
+    const dim3 grid((width + 31) / 32, (out_rows + 7) / 8);
+    guide_generic_kernel<<<grid, block, 0, stream>>>(blurred, rtv, guide, width, height, ksize, src_y0, src_rows, dst_y0,
+                                                    out_y0, out_rows);
     return cudaGetLastError();
 }
 

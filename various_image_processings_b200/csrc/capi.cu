@@ -481,9 +481,11 @@ int vip_btf_iterate_strip(vip_btf* f, const uint8_t* d_src_n, uint8_t* d_dst_n, 
     float* rt = static_cast<float*>(f->rtv.p);
     uint8_t* gd = static_cast<uint8_t*>(f->guide.p);
     cudaError_t e;
-    if ((e = vip::launch_gradient_u8(d_src_n, mag, W, H, 3, base, s->src_rows, base, m0, m1 - m0, st)) != cudaSuccess)
-        return cu(e);
-    if ((e = vip::launch_blur_rtv(d_src_n, mag, bl, rt, W, H, k, base, s->src_rows, base, b0, b1 - b0, st)) !=
+    // the gradient stage (:207) is fused into blur / mRTV: magnitude == nullptr computes it from the image tile
+    (void)mag;
+    (void)m0;
+    (void)m1;
+    if ((e = vip::launch_blur_rtv(d_src_n, nullptr, bl, rt, W, H, k, base, s->src_rows, base, b0, b1 - b0, st)) !=
         cudaSuccess)
         return cu(e);
     if ((e = vip::launch_guide(bl, rt, gd, W, H, k, base, s->src_rows, base, g0, g1 - g0, st)) != cudaSuccess)
