@@ -211,9 +211,9 @@ def main():
     # ---- work decomposition
     strong = (filt == "bf" and args.workload == "bf_8k_r15" and world > 1)
     if strong:
-        y0, y1 = h * rank // world, h * (rank + 1) // world
-        s0, s1 = max(0, y0 - radius), min(h, y1 + radius)
-        strip = vip.Strip(s0, s1 - s0, y0, y0, y1 - y0)
+        plan = vip.plan_strips(h, world, vip.halo_rows("bf", ksize))[rank]
+        y0, y1, s0, s1 = plan
+        strip = vip.to_strip(plan)
     else:
         y0, y1, s0, s1 = 0, h, 0, h
         strip = None

@@ -6,6 +6,7 @@ Python mirror of the reference's host interface.  There is no CPU fallback.
 """
 from . import capi
 from .capi import Strip, VipError, launch_count
+from .strips import StripPlan, halo_rows, plan_strips, to_strip
 from .filters import (CudaAdaptiveBilateralFilter, CudaBilateralFilter, CudaBilateralTextureFilter, CudaIntegralImage,
                       DeviceImage, MultiGpuFilter, PinnedBuffer, cuda_gradient, cuda_gradient_strip,
                       device_synchronize)
@@ -13,5 +14,5 @@ from .filters import (CudaAdaptiveBilateralFilter, CudaBilateralFilter, CudaBila
 __all__ = [
     "capi", "Strip", "VipError", "launch_count", "CudaAdaptiveBilateralFilter", "CudaBilateralFilter",
     "CudaBilateralTextureFilter", "CudaIntegralImage", "DeviceImage", "MultiGpuFilter", "PinnedBuffer",
-    "cuda_gradient", "cuda_gradient_strip", "device_synchronize",
+    "cuda_gradient", "cuda_gradient_strip", "device_synchronize", "StripPlan", "halo_rows", "plan_strips", "to_strip",
 ]
