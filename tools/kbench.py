@@ -15,7 +15,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import _oracle as O  # noqa: E402
 import various_image_processings_b200 as vip  # noqa: E402
 
-DEFAULT = ["bf:3840x2160:11", "abf:3840x2160:15", "jbf:3840x2160:17", "bf:7680x4320:31", "btf:3840x2160:9", "bf:1920x1080:9", "abf:1920x1080:9"]
+DEFAULT = ["bf:3840x2160:11", "abf:3840x2160:15", "jbf:3840x2160:17", "bf:7680x4320:31", "btf:3840x2160:9", "bf:1920x1080:9", "abf:1920x1080:9", "grad:3840x2160:3", "integral:3840x2160:7"]
 
 
 def taps(r):
@@ -52,6 +52,32 @@ def main():
         d_src, d_guide = torch.from_numpy(img).cuda(), torch.from_numpy(guide).cuda()
         d_dst, d_ref = torch.empty_like(d_src), torch.empty_like(d_src)
         ref_ms = float("nan")
+        if kind in ("grad", "integral"):
+            # streaming stages: report achieved GB/s of algorithmic bytes (k = channels for grad, radius for integral)
+            if kind == "grad":
+                g = torch.empty((h, w), dtype=torch.float32, device="cuda")
+                run = lambda: vip.cuda_gradient(d_src, g, w, h, 3)
+                nbytes = w * h * 7
+                same = "n/a"
+                if R:
+                    gr = torch.empty_like(g)
+                    R.refcu_gradient_u8(d_src.data_ptr(), gr.data_ptr(), w, h, 3)
+                    run()
+                    torch.cuda.synchronize()
+                    same = "EXACT" if torch.equal(g, gr) else "DIFF"
+            else:
+                ii = vip.CudaIntegralImage(w, h, k)
+                run = lambda: ii.build(d_src)
+                nbytes = (w + 2 * k + 1) * (h + 2 * k + 1) * 15
+                run()
+                torch.cuda.synchronize()
+                tab = ii.download_table().reshape(h + 2 * k + 1, w + 2 * k + 1, 3)
+                pad = np.pad(img[:64].astype(np.uint64), ((k, 0), (k, k), (0, 0)), mode="edge")
+                want = np.cumsum(np.cumsum(pad, 0), 1).astype(np.uint32)
+                same = "EXACT(top rows)" if np.array_equal(tab[1:1 + pad.shape[0], 1:], want) else "DIFF"
+            ms = timed(run)
+            print(f"{spec:22s} {ms:8.3f} ms  {w * h / ms / 1e3:9.0f} Mpix/s  {nbytes / ms / 1e6:8.1f} GB/s algorithmic  {same}", flush=True)
+            continue
         if kind in ("bf", "jbf"):
             f = vip.CudaBilateralFilter(w, h, k)
             run = (lambda: f.bilateral_filter_async(d_src, d_dst)) if kind == "bf" else (lambda: f.joint_bilateral_filter_async(d_src, d_guide, d_dst))
