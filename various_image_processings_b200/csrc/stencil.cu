@@ -34,8 +34,10 @@
 namespace vip {
 namespace {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 256;            // threads of one warp group (one tile in flight per group)
 constexpr int kWarps = kThreads / 32;
+constexpr int kMaxGroups = 3;            // warp groups per CTA: 24 warps / SM, <= 80 registers per thread
+constexpr int kSmemBudget = 232448 - 1024;  // opt-in maximum of dynamic shared memory per CTA (227 KB) minus the driver's 1 KB
 constexpr int kTileRows = 32;  // one lane per output row
 constexpr int kMaxTiledRadius = 15;
 
@@ -186,11 +188,11 @@ __device__ __forceinline__ void do_row(int len, const typename Elem<MODE>::type*
 }
 
 struct SmemLayout {
-    int lut_off, w_off, hw_off, tile_off, hs_off, total;
-    int tile_pitch, tile_w, tile_h, hs_pitch, w_pitch;
+    int lut_off, w_off, hw_off, sched_off, tile_off, hs_off, total;   // tile_off / hs_off: group 0; group g adds g * group_stride
+    int tile_pitch, tile_w, tile_h, hs_pitch, w_pitch, group_stride;
 };
 
-__host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, int lut_n) {
+__host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, int lut_n, int n_groups) {
     SmemLayout L;
     const int k = 2 * radius + 1;
     L.tile_w = kWarps * P + 2 * radius;
@@ -206,40 +208,51 @@ __host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, i
     L.hw_off = off;
     off += k * 4;
     off = (off + 15) & ~15;
+    L.sched_off = off;  // tile counter of the CTA + the tile each group is working on
+    off += 16;
     L.tile_off = off;
     off += L.tile_pitch * L.tile_h * (mode == kJBF ? 8 : 4);
     off = (off + 15) & ~15;
     L.hs_off = off;
     if (mode == kABF) off += L.hs_pitch * L.tile_h * 8;
-    L.total = off;
+    off = (off + 15) & ~15;
+    L.group_stride = off - L.tile_off;
+    L.total = L.tile_off + n_groups * L.group_stride;
     return L;
 }
 
 template <int MODE, int P, bool CLAMP>
-__global__ void __launch_bounds__(kThreads, 2) stencil_kernel(const StencilArgs a, const int tiles_x, const int n_tiles) {
+__global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
+    stencil_kernel(const StencilArgs a, const int tiles_x, const int n_tiles) {
     using E = typename Elem<MODE>::type;
     extern __shared__ __align__(16) unsigned char smem[];
     const int radius = a.radius;
     const int k = 2 * radius + 1;
-    const SmemLayout L = make_layout(MODE, P, radius, a.lut_n);
+    const int n_groups = blockDim.x / kThreads;
+    const int group = threadIdx.x / kThreads;  // warp group: its own tile buffer, named barrier and tile sequence
+    const SmemLayout L = make_layout(MODE, P, radius, a.lut_n, n_groups);
     float* const lut_s = reinterpret_cast<float*>(smem + L.lut_off);
     float* const w_s = reinterpret_cast<float*>(smem + L.w_off);
     int* const hw_s = reinterpret_cast<int*>(smem + L.hw_off);
-    E* const tile = reinterpret_cast<E*>(smem + L.tile_off);
-    uint2* const hs = reinterpret_cast<uint2*>(smem + L.hs_off);
+    int* const sched = reinterpret_cast<int*>(smem + L.sched_off);
+    E* const tile = reinterpret_cast<E*>(smem + L.tile_off + group * L.group_stride);
+    uint2* const hs = reinterpret_cast<uint2*>(smem + L.hs_off + group * L.group_stride);
 
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x - group * kThreads;
     const int lane = tid & 31;
     const int warp = tid >> 5;
+    auto group_sync = [&]() { asm volatile("bar.sync %0, %1;" ::"r"(group + 1), "n"(kThreads) : "memory"); };
 
-    // one-time per CTA: replicated LUT, spatial half rows, half widths
-    for (int i = tid; i < a.lut_n * 32; i += kThreads) lut_s[i] = __ldg(a.lut + (i >> 5));
-    for (int i = tid; i < k * L.w_pitch; i += kThreads) {
+    // one-time per CTA (shared by all groups): replicated LUT, spatial weight rows, half widths
+    for (int i = threadIdx.x; i < a.lut_n * 32; i += blockDim.x) lut_s[i] = __ldg(a.lut + (i >> 5));
+    for (int i = threadIdx.x; i < k * L.w_pitch; i += blockDim.x) {
         const int row = i / L.w_pitch, j = i - row * L.w_pitch;
         const int hw = __ldg(a.hw + row);
         w_s[i] = j <= 2 * hw ? __ldg(a.ks_full + row * k + (radius - hw + j)) : 0.f;
     }
-    for (int i = tid; i < k; i += kThreads) hw_s[i] = __ldg(a.hw + i);
+    for (int i = threadIdx.x; i < k; i += blockDim.x) hw_s[i] = __ldg(a.hw + i);
+    if (threadIdx.x == 0) sched[0] = 0;
+    __syncthreads();
 
     // byte address of this lane's copy of entry 0; ABF folds the 2^23 bias of its index trick in (see run_taps)
     const std::uint32_t lut_addr = static_cast<std::uint32_t>(__cvta_generic_to_shared(lut_s + lane)) -
@@ -250,17 +263,24 @@ __global__ void __launch_bounds__(kThreads, 2) stencil_kernel(const StencilArgs 
     const int tw = L.tile_w, th = L.tile_h, tp = L.tile_pitch;
     const int step_x = kThreads % tw, step_y = kThreads / tw;
 
-    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+    // Tiles blockIdx.x, blockIdx.x + gridDim.x, ... belong to this CTA (every SM gets the same number +-1); its warp
+    // groups take them in order from a shared-memory counter, so a group that finishes early picks up the next tile.
+    for (;;) {
+        group_sync();  // previous tile of this group fully consumed (tile buffer and sched slot reusable)
+        if (tid == 0) sched[1 + group] = atomicAdd(&sched[0], 1);
+        group_sync();
+        const int t = blockIdx.x + sched[1 + group] * gridDim.x;
+        if (t >= n_tiles) break;
         const int tile_x = t % tiles_x, tile_y = t / tiles_x;
         const int X0 = tile_x * (kWarps * P);
         const int Y0 = a.out_y0 + tile_y * kTileRows;
 
-        __syncthreads();  // previous tile fully consumed (and, first time round, the tables are written)
         {
             int ex = tid % tw, ey = tid / tw;
             while (ey < th) {
                 const int gx = clampi(X0 - radius + ex, 0, W - 1);
-                const int gy = clampi(Y0 - radius + ey, 0, H - 1) - a.src_y0;
+                // clamp to the image, then (rows no valid output depends on) to the rows the buffers hold
+                const int gy = clampi(clampi(Y0 - radius + ey, 0, H - 1), a.src_y0, a.src_y0 + a.src_rows - 1) - a.src_y0;
                 const size_t o = (static_cast<size_t>(gy) * W + gx) * 3;
                 if constexpr (MODE == kJBF) {
                     tile[ey * tp + ex] = make_uint2(load_packed(a.guide + o), load_packed(a.src + o));
@@ -275,7 +295,7 @@ __global__ void __launch_bounds__(kThreads, 2) stencil_kernel(const StencilArgs 
                 }
             }
         }
-        __syncthreads();
+        group_sync();
 
         if constexpr (MODE == kABF) {
             // horizontal k-sums of every tile row for the 8P output columns: hs[row][col] = {B | R<<16, G}
@@ -299,7 +319,7 @@ __global__ void __launch_bounds__(kThreads, 2) stencil_kernel(const StencilArgs 
                     hr[j] = make_uint2(br, g);
                 }
             }
-            __syncthreads();
+            group_sync();
         }
 
         Acc<MODE, P> A;
@@ -450,22 +470,33 @@ __global__ void stencil_generic_kernel(const StencilArgs a, const int lut_len) {
     d[2] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(s2, sk), 0.5f));
 }
 
-template <int MODE, int P, bool CLAMP>
+// outputs per thread: ABF keeps 6 more floats per output alive (centre, offset), so it runs 4 wide to stay within the
+// 80 registers that 24 warps per SM allow
+constexpr int outputs_per_thread(int mode) { return mode == kABF ? 4 : 8; }
+
+// Warp groups per CTA that fit the shared-memory budget with `lut_n` replicated entries (0: none).
+int groups_that_fit(int mode, int radius, int lut_n) {
+    for (int g = kMaxGroups; g >= 1; --g)
+        if (make_layout(mode, outputs_per_thread(mode), radius, lut_n, g).total <= kSmemBudget) return g;
+    return 0;
+}
+
+template <int MODE, bool CLAMP>
 cudaError_t launch_tiled(const StencilArgs& a, int sm_count, cudaStream_t stream) {
-    const SmemLayout L = make_layout(MODE, P, a.radius, a.lut_n);
+    constexpr int P = outputs_per_thread(MODE);
+    const int n_groups = groups_that_fit(MODE, a.radius, a.lut_n);
+    if (n_groups < 1) return cudaErrorInvalidConfiguration;
+    const SmemLayout L = make_layout(MODE, P, a.radius, a.lut_n, n_groups);
     auto kern = stencil_kernel<MODE, P, CLAMP>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total);
     if (e != cudaSuccess) return e;
     const int tiles_x = (a.width + kWarps * P - 1) / (kWarps * P);
     const int tiles_y = (a.out_rows + kTileRows - 1) / kTileRows;
     const int n_tiles = tiles_x * tiles_y;
-    int per_sm = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, L.total);
-    if (e != cudaSuccess) return e;
-    if (per_sm < 1) return cudaErrorInvalidConfiguration;
-    int grid = sm_count * per_sm;
+    // one persistent CTA per SM
+    int grid = sm_count;
     if (grid > n_tiles) grid = n_tiles;
-    kern<<<grid, kThreads, L.total, stream>>>(a, tiles_x, n_tiles);
+    kern<<<grid, kThreads * n_groups, L.total, stream>>>(a, tiles_x, n_tiles);
     count_launch();
     return cudaGetLastError();
 }
@@ -484,14 +515,16 @@ cudaError_t launch_generic(const StencilArgs& a, cudaStream_t stream) {
 int stencil_max_tiled_radius() { return kMaxTiledRadius; }
 
 void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, int* lut_n, int* clamp) {
-    // Two resident CTAs per SM: 2 * (dynamic + 1 KB reserved) <= 228 KB.
-    constexpr int kTwoCtaBudget = (233472 / 2) - 1024;
+    // The whole table, replicated 32x, is shared by the warp groups of the one CTA an SM runs: when it fits next to
+    // kMaxGroups tile buffers no index clamp is needed.  Otherwise trailing zeros are cut: every index > last_nz has
+    // weight exactly 0, so clamping the index to last_nz+1 (a zero entry) is bit-neutral.
     *lut_n = table_len;
     *clamp = 0;
     if (radius > kMaxTiledRadius) return;
     const bool zero_tail = last_nz + 1 < table_len;
-    if (make_layout(mode, 8, radius, table_len).total <= kTwoCtaBudget || !zero_tail) return;
-    *lut_n = last_nz + 2;  // entry last_nz+1 is 0 and stands for every larger index
+    if (groups_that_fit(mode, radius, table_len) == kMaxGroups || !zero_tail) return;
+    if (groups_that_fit(mode, radius, last_nz + 2) <= groups_that_fit(mode, radius, table_len)) return;
+    *lut_n = last_nz + 2;
     *clamp = 1;
 }
 
@@ -507,14 +540,11 @@ cudaError_t launch_stencil(StencilMode mode, const StencilArgs& a, int sm_count,
     const bool clamp = a.lut_clamp != 0;
     switch (mode) {
         case kBF:
-            return clamp ? launch_tiled<kBF, 8, true>(a, sm_count, stream)
-                         : launch_tiled<kBF, 8, false>(a, sm_count, stream);
+            return clamp ? launch_tiled<kBF, true>(a, sm_count, stream) : launch_tiled<kBF, false>(a, sm_count, stream);
         case kJBF:
-            return clamp ? launch_tiled<kJBF, 8, true>(a, sm_count, stream)
-                         : launch_tiled<kJBF, 8, false>(a, sm_count, stream);
+            return clamp ? launch_tiled<kJBF, true>(a, sm_count, stream) : launch_tiled<kJBF, false>(a, sm_count, stream);
         default:
-            return clamp ? launch_tiled<kABF, 8, true>(a, sm_count, stream)
-                         : launch_tiled<kABF, 8, false>(a, sm_count, stream);
+            return clamp ? launch_tiled<kABF, true>(a, sm_count, stream) : launch_tiled<kABF, false>(a, sm_count, stream);
     }
 }
 
