@@ -28,6 +28,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <type_traits>
 
 #include "vip_internal.h"
 
@@ -52,8 +53,9 @@ struct Elem<kJBF> {
 
 // Packed fp32x2 (sm_100 FFMA2): {s0,s1} and {s2,sk} accumulate with one instruction each; sk = fma(1, w, sk) is the
 // same rounding as sk + w.  The multiplier w is a scalar operand broadcast to both halves (FFMA2 Rd, Ra.F32x2, Rb.F32, Rd).
-// Measured on B200 (tools/kbench.py): FFMA2 issues at half the FFMA rate, so this only trades issue slots for
-// nothing on the FMA pipe: +3 % for BF/JBF (ALU-pipe heavy), -2 % for ABF (FMA-pipe heavy) -> used for BF/JBF only.
+// Measured on B200 (tools/kbench.py): a packed instruction occupies the dispatch port like two scalar ones, so it buys
+// registers-file traffic and code size, not issue cycles: +3 % for BF/JBF.  ABF packs across two adjacent OUTPUTS
+// instead (see Acc<kABF>): +4 % (4K r=7: 0.867 -> 0.833 ms).
 template <int MODE>
 struct UseFma2 {
     static constexpr bool value = MODE != kABF;
@@ -70,14 +72,28 @@ __device__ __forceinline__ void fma2(unsigned long long& acc, const unsigned lon
     asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
 }
 
+__device__ __forceinline__ unsigned long long add2(const unsigned long long a, const unsigned long long b) {
+    unsigned long long r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
 template <int MODE, int P>
 struct Acc {
     float s0[UseFma2<MODE>::value ? 1 : P], s1[UseFma2<MODE>::value ? 1 : P], s2[UseFma2<MODE>::value ? 1 : P],
         sk[UseFma2<MODE>::value ? 1 : P];
     unsigned long long s01[UseFma2<MODE>::value ? P : 1], s2k[UseFma2<MODE>::value ? P : 1];
     std::uint32_t c[P];             // BF/JBF: packed centre (range source)
-    float fp[MODE == kABF ? 3 : 1][P];   // ABF: centre as float
-    float off[MODE == kABF ? 3 : 1][P];  // ABF: centre - box mean
+};
+
+// ABF: every quantity is a pair over two horizontally adjacent outputs (2p, 2p+1), so that one packed fp32x2
+// instruction serves two taps: the neighbour value is the broadcast scalar operand, the per-output values
+// (-centre, -offset, weights, sums) are the packed ones.
+template <int P>
+struct Acc<kABF, P> {
+    unsigned long long s[4][P / 2];     // s0, s1, s2, sk
+    unsigned long long nfp[3][P / 2];   // -(centre as float), per channel
+    unsigned long long noff[3][P / 2];  // -(centre - box mean)
 };
 
 __device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
@@ -140,17 +156,7 @@ __device__ __forceinline__ void run_taps(const typename Elem<MODE>::type* __rest
             const int j = n - i;
             if (j >= 0 && j < L) {
                 std::uint32_t addr;
-                if constexpr (MODE == kABF) {
-                    // src/adaptive_bilateral_filter_impl.cu:67-73: neighbour - centre - offset, float abs, left-to-right sum
-                    const float d0 = __fsub_rn(__fsub_rn(f0, A.fp[0][i]), A.off[0][i]);
-                    const float d1 = __fsub_rn(__fsub_rn(f1, A.fp[1][i]), A.off[1][i]);
-                    const float d2 = __fsub_rn(__fsub_rn(f2, A.fp[2][i]), A.off[2][i]);
-                    float dist = __fadd_rn(__fadd_rn(fabsf(d0), fabsf(d1)), fabsf(d2));
-                    if constexpr (CLAMP) dist = fminf(dist, clamp_f);
-                    // (int)dist: bits(dist +rz 2^23) = 0x4b000000 + floor(dist); << 7 leaves 0x80000000 + 128*floor(dist),
-                    // and lut_addr already carries the -0x80000000 (32-bit wrap-around)
-                    addr = lut_addr + (__float_as_uint(__fadd_rz(dist, 8388608.f)) << 7);
-                } else {
+                {
                     std::uint32_t sad = __vsadu4(q, A.c[i]);
                     if constexpr (CLAMP) sad = min(sad, clamp_i);
                     addr = lut_addr + (sad << 7);
@@ -171,18 +177,112 @@ __device__ __forceinline__ void run_taps(const typename Elem<MODE>::type* __rest
     }
 }
 
+// ABF weight of one tap from its three shifted differences (src/adaptive_bilateral_filter_impl.cu:67-73, 103-105)
+template <bool CLAMP>
+__device__ __forceinline__ float abf_weight(const float d0, const float d1, const float d2, const float ks,
+                                            const std::uint32_t lut_addr, const float clamp_f) {
+    float dist = __fadd_rn(__fadd_rn(fabsf(d0), fabsf(d1)), fabsf(d2));
+    if constexpr (CLAMP) dist = fminf(dist, clamp_f);
+    // (int)dist: bits(dist +rz 2^23) = 0x4b000000 + floor(dist); << 7 leaves 0x80000000 + 128*floor(dist),
+    // and lut_addr already carries the -0x80000000 (32-bit wrap-around)
+    const std::uint32_t addr = lut_addr + (__float_as_uint(__fadd_rz(dist, 8388608.f)) << 7);
+    return __fmul_rn(ks, lds_f32(addr));
+}
+
+// ABF run: outputs are handled in pairs (2p, 2p+1).  Neighbour n is tap j = n - 2p of the first and tap j - 1 of
+// the second output; when both are inside the run the differences and the four accumulations are packed fp32x2
+// operations (same IEEE roundings per half as the scalar ones), otherwise the one valid output goes scalar.
+template <int P, int L, bool CLAMP>
+__device__ __forceinline__ void run_taps_abf(const std::uint32_t* __restrict__ t, const float* __restrict__ wp,
+                                             const std::uint32_t lut_addr, const float clamp_f, Acc<kABF, P>& A) {
+    float w[(L + 3) & ~3];
+#pragma unroll
+    for (int j = 0; j < (L + 3) / 4; ++j) {
+        const float4 v = reinterpret_cast<const float4*>(wp)[j];
+        w[4 * j + 0] = v.x;
+        w[4 * j + 1] = v.y;
+        w[4 * j + 2] = v.z;
+        w[4 * j + 3] = v.w;
+    }
+    const unsigned long long one2 = pack2(1.f, 1.f);
+#pragma unroll
+    for (int n = 0; n < P + L - 1; ++n) {
+        const std::uint32_t v = t[n];
+        const float f0 = byte_to_float<0>(v);
+        const float f1 = byte_to_float<1>(v);
+        const float f2 = byte_to_float<2>(v);
+#pragma unroll
+        for (int p = 0; p < P / 2; ++p) {
+            const int j = n - 2 * p;  // tap of output 2p; output 2p+1 sees tap j-1
+            const bool lo = j >= 0 && j < L, hi = j - 1 >= 0 && j - 1 < L;
+            if (lo && hi) {
+                const unsigned long long d0 = add2(add2(pack2(f0, f0), A.nfp[0][p]), A.noff[0][p]);
+                const unsigned long long d1 = add2(add2(pack2(f1, f1), A.nfp[1][p]), A.noff[1][p]);
+                const unsigned long long d2 = add2(add2(pack2(f2, f2), A.nfp[2][p]), A.noff[2][p]);
+                float d0l, d0h, d1l, d1h, d2l, d2h;
+                unpack2(d0, d0l, d0h);
+                unpack2(d1, d1l, d1h);
+                unpack2(d2, d2l, d2h);
+                const float wl = abf_weight<CLAMP>(d0l, d1l, d2l, w[j], lut_addr, clamp_f);
+                const float wh = abf_weight<CLAMP>(d0h, d1h, d2h, w[j - 1], lut_addr, clamp_f);
+                const unsigned long long ww = pack2(wl, wh);
+                fma2(A.s[0][p], ww, pack2(f0, f0));
+                fma2(A.s[1][p], ww, pack2(f1, f1));
+                fma2(A.s[2][p], ww, pack2(f2, f2));
+                fma2(A.s[3][p], ww, one2);
+            } else if (lo || hi) {
+                const int jj = lo ? j : j - 1;
+                float nf[3], no[3], a[4], other[4];
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    float x, y;
+                    unpack2(A.nfp[c][p], x, y);
+                    nf[c] = lo ? x : y;
+                    unpack2(A.noff[c][p], x, y);
+                    no[c] = lo ? x : y;
+                }
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    float x, y;
+                    unpack2(A.s[c][p], x, y);
+                    a[c] = lo ? x : y;
+                    other[c] = lo ? y : x;
+                }
+                const float d0 = __fadd_rn(__fadd_rn(f0, nf[0]), no[0]);
+                const float d1 = __fadd_rn(__fadd_rn(f1, nf[1]), no[1]);
+                const float d2 = __fadd_rn(__fadd_rn(f2, nf[2]), no[2]);
+                const float wt = abf_weight<CLAMP>(d0, d1, d2, w[jj], lut_addr, clamp_f);
+                a[0] = __fmaf_rn(f0, wt, a[0]);
+                a[1] = __fmaf_rn(f1, wt, a[1]);
+                a[2] = __fmaf_rn(f2, wt, a[2]);
+                a[3] = __fadd_rn(a[3], wt);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) A.s[c][p] = lo ? pack2(a[c], other[c]) : pack2(other[c], a[c]);
+            }
+        }
+    }
+}
+
 // One window row of len = 2*hw+1 taps: runs of 8, then the odd remainder.
 template <int MODE, int P, bool CLAMP>
 __device__ __forceinline__ void do_row(int len, const typename Elem<MODE>::type* __restrict__ t,
                                        const float* __restrict__ wp, const std::uint32_t lut_addr,
                                        const std::uint32_t clamp_i, const float clamp_f, Acc<MODE, P>& A) {
+    auto run = [&](auto lc) {
+        constexpr int L = decltype(lc)::value;
+        if constexpr (MODE == kABF) {
+            run_taps_abf<P, L, CLAMP>(t, wp, lut_addr, clamp_f, A);
+        } else {
+            run_taps<MODE, P, L, CLAMP>(t, wp, lut_addr, clamp_i, clamp_f, A);
+        }
+    };
 #pragma unroll 1
-    for (; len >= 8; len -= 8, t += 8, wp += 8) run_taps<MODE, P, 8, CLAMP>(t, wp, lut_addr, clamp_i, clamp_f, A);
+    for (; len >= 8; len -= 8, t += 8, wp += 8) run(std::integral_constant<int, 8>{});
     switch (len) {
-        case 7: run_taps<MODE, P, 7, CLAMP>(t, wp, lut_addr, clamp_i, clamp_f, A); break;
-        case 5: run_taps<MODE, P, 5, CLAMP>(t, wp, lut_addr, clamp_i, clamp_f, A); break;
-        case 3: run_taps<MODE, P, 3, CLAMP>(t, wp, lut_addr, clamp_i, clamp_f, A); break;
-        case 1: run_taps<MODE, P, 1, CLAMP>(t, wp, lut_addr, clamp_i, clamp_f, A); break;
+        case 7: run(std::integral_constant<int, 7>{}); break;
+        case 5: run(std::integral_constant<int, 5>{}); break;
+        case 3: run(std::integral_constant<int, 3>{}); break;
+        case 1: run(std::integral_constant<int, 1>{}); break;
         default: break;
     }
 }
@@ -324,24 +424,11 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
 
         Acc<MODE, P> A;
         const E* const tcentre = tile + (lane + radius) * tp + (warp * P + radius);
+        if constexpr (MODE == kABF) {
+            float nfp[3][P], noff[3][P];
 #pragma unroll
-        for (int i = 0; i < P; ++i) {
-            if constexpr (UseFma2<MODE>::value) {
-                A.s01[i] = 0ull;
-                A.s2k[i] = 0ull;
-            } else {
-                A.s0[i] = 0.f;
-                A.s1[i] = 0.f;
-                A.s2[i] = 0.f;
-                A.sk[i] = 0.f;
-            }
-            if constexpr (MODE == kJBF) {
-                A.c[i] = tcentre[i].x;
-            } else if constexpr (MODE == kBF) {
-                A.c[i] = tcentre[i];
-            } else {
+            for (int i = 0; i < P; ++i) {
                 const std::uint32_t c = tcentre[i];
-                A.c[i] = c;
                 std::uint32_t sb = 0, sg = 0, sr = 0;
                 const uint2* hcol = hs + lane * L.hs_pitch + warp * P + i;
                 for (int j = 0; j < k; ++j) {
@@ -353,13 +440,41 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
                 const float kk = static_cast<float>(k * k);
                 const float c0 = static_cast<float>(c & 0xffu), c1 = static_cast<float>((c >> 8) & 0xffu),
                             c2 = static_cast<float>((c >> 16) & 0xffu);
-                A.fp[0][i] = c0;
-                A.fp[1][i] = c1;
-                A.fp[2][i] = c2;
-                // src/adaptive_bilateral_filter_impl.cu:88-93: centre - sum / (ksize*ksize)
-                A.off[0][i] = __fsub_rn(c0, __fdiv_rn(static_cast<float>(sb), kk));
-                A.off[1][i] = __fsub_rn(c1, __fdiv_rn(static_cast<float>(sg), kk));
-                A.off[2][i] = __fsub_rn(c2, __fdiv_rn(static_cast<float>(sr), kk));
+                nfp[0][i] = -c0;
+                nfp[1][i] = -c1;
+                nfp[2][i] = -c2;
+                // src/adaptive_bilateral_filter_impl.cu:88-93: centre - sum / (ksize*ksize); kept negated (x - y == x + (-y))
+                noff[0][i] = -__fsub_rn(c0, __fdiv_rn(static_cast<float>(sb), kk));
+                noff[1][i] = -__fsub_rn(c1, __fdiv_rn(static_cast<float>(sg), kk));
+                noff[2][i] = -__fsub_rn(c2, __fdiv_rn(static_cast<float>(sr), kk));
+            }
+#pragma unroll
+            for (int p2 = 0; p2 < P / 2; ++p2) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    A.nfp[c][p2] = pack2(nfp[c][2 * p2], nfp[c][2 * p2 + 1]);
+                    A.noff[c][p2] = pack2(noff[c][2 * p2], noff[c][2 * p2 + 1]);
+                }
+#pragma unroll
+                for (int c = 0; c < 4; ++c) A.s[c][p2] = 0ull;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < P; ++i) {
+                if constexpr (UseFma2<MODE>::value) {
+                    A.s01[i] = 0ull;
+                    A.s2k[i] = 0ull;
+                } else {
+                    A.s0[i] = 0.f;
+                    A.s1[i] = 0.f;
+                    A.s2[i] = 0.f;
+                    A.sk[i] = 0.f;
+                }
+                if constexpr (MODE == kJBF) {
+                    A.c[i] = tcentre[i].x;
+                } else {
+                    A.c[i] = tcentre[i];
+                }
             }
         }
 
@@ -378,7 +493,13 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
 #pragma unroll
             for (int i = 0; i < P; ++i) {
                 float s0, s1, s2, sk;
-                if constexpr (UseFma2<MODE>::value) {
+                if constexpr (MODE == kABF) {
+                    float x[4], y[4];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) unpack2(A.s[c][i / 2], x[c], y[c]);
+                    s0 = (i & 1) ? y[0] : x[0], s1 = (i & 1) ? y[1] : x[1], s2 = (i & 1) ? y[2] : x[2],
+                    sk = (i & 1) ? y[3] : x[3];
+                } else if constexpr (UseFma2<MODE>::value) {
                     unpack2(A.s01[i], s0, s1);
                     unpack2(A.s2k[i], s2, sk);
                 } else {
