@@ -38,7 +38,7 @@ WORKLOADS = {
     "abf_4k_r7": ("abf", 3840, 2160, 15, 0, "adaptive bilateral filter radius=7 on synthetic 3840x2160 RGB (BASELINE configs[1])"),
     "btf_4k": ("btf", 3840, 2160, 9, 3, "bilateral texture filter k=9, 3 iterations on synthetic 3840x2160 RGB (configs[2])"),
     "bf_8k_r15": ("bf", 7680, 4320, 31, 0, "bilateral filter radius=15 on synthetic 7680x4320 RGB, row strips + halos (configs[3])"),
-    "bf_lenna": ("bf", 512, 512, 11, 0, "bilateral filter radius=5 on a 512x512 RGB image (configs[0] geometry)"),
+    "bf_lenna": ("bf", 512, 512, 11, 0, "bilateral filter radius=5 on sample_image/lenna.png 512x512 BGR (configs[0]; committed fixture)"),
     "bf_4k_r5": ("bf", 3840, 2160, 11, 0, "bilateral filter radius=5 on synthetic 3840x2160 RGB"),
     "bf_1080p": ("bf", 1920, 1080, 9, 0, "bilateral filter k=9 on 1080p frames (configs[4])"),
     "abf_1080p": ("abf", 1920, 1080, 9, 0, "adaptive bilateral filter k=9 on 1080p frames (configs[4])"),
@@ -54,6 +54,11 @@ def mask_taps(r):
 def synth_frame(w, h, seed):
     """S-rand: i.i.d. uniform bytes (content-independent, like the reference's test fixtures)."""
     return np.random.RandomState(seed).randint(0, 256, size=(h, w, 3), dtype=np.uint8)
+
+
+def lenna_frame():
+    """configs[0]: sample_image/lenna.png decoded to BGR (committed fixture, tests/golden/make_golden_lenna.py)."""
+    return np.ascontiguousarray(np.load(os.path.join(ROOT, "tests", "golden", "lenna_vectors.npz"))["lenna_bgr"])
 
 
 class ClockSampler:
@@ -103,7 +108,7 @@ class ClockSampler:
 def cpu_reference(filt, w, h, ksize, nitr, sample_rows, threads, repeats=1):
     """The reference's own CPU path on a full-width crop of `sample_rows` rows; returns (Mpixel/s, kind, cores, what)."""
     import _oracle as O
-    img = synth_frame(w, sample_rows, 42)
+    img = np.ascontiguousarray(lenna_frame()[:sample_rows]) if (w, h, filt) == (512, 512, "bf") else synth_frame(w, sample_rows, 42)
     dst = np.empty_like(img)
     if O.have_ref_cpu():
         R = O.ref_cpu()
@@ -222,7 +227,9 @@ def main():
     # inputs resident in HBM; rotate over enough distinct frames that in+out exceed the L2
     n_pool = max(2, int(np.ceil(1.2 * L2_BYTES / (2.0 * w * (s1 - s0) * 3))))
     n_pool = min(n_pool, 16)
-    if args.content == "rand":
+    if args.workload == "bf_lenna":
+        frames = [lenna_frame()] * n_pool
+    elif args.content == "rand":
         frames = [synth_frame(w, h, 42 + 1000 * rank + i) for i in range(n_pool)]
     else:
         import _oracle as O

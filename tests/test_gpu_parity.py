@@ -92,6 +92,32 @@ def test_abf_reference_fixture(vip, k, key):
     assert maxdiff(got, G[key]) <= 1
 
 
+# ------------------------------------------------------------------ BASELINE configs[0]: lenna.png, BF radius 5
+LENNA = np.load(os.path.join(os.path.dirname(__file__), "golden", "lenna_vectors.npz"))
+
+
+def test_lenna_bf_r5(vip):
+    """configs[0]: 512x512 lenna, ksize 11.  Exact vs the CUDA-arithmetic oracle; <= 1 LSB vs the reference's C++ CPU
+    path (its LUTs are built in double); exact vs that CPU path's arithmetic up to FMA contraction when
+    the CPU LUT formula is selected (still <= 1 LSB, and only a handful of pixels differ)."""
+    img = LENNA["lenna_bgr"]
+    got = run_bf(vip, img, 11)
+    assert np.array_equal(got, O.o_bf(img, 11))
+    assert maxdiff(got, LENNA["bf_r5_cpu"]) <= 1
+    assert (got != LENNA["bf_r5_cpu"]).mean() < 0.01
+    got2 = run_bf(vip, img, 11, lut_mode=vip.capi.VIP_LUT_CPU)
+    assert maxdiff(got2, LENNA["bf_r5_cpu"]) <= 1
+
+
+def test_lenna_crop_abf_btf(vip):
+    crop = np.ascontiguousarray(LENNA["lenna_bgr"][128:384, 128:384])
+    got = run_abf(vip, crop, 15)
+    assert np.array_equal(got, O.o_abf(crop, 15))
+    assert maxdiff(got, LENNA["abf_r7_crop_cpu"]) <= 1
+    got = run_btf(vip, crop, 9, 3)
+    assert np.array_equal(got, O.o_btf(crop, 9, 3))
+
+
 # ------------------------------------------------------------------ sizes, radii, sigmas, content
 SIZES = [(1, 1), (5, 7), (50, 50), (64, 32), (65, 33), (131, 70), (257, 19)]
 

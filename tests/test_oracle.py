@@ -126,3 +126,20 @@ def test_live_against_reference_cpu_build(w, h, k):
     if k <= 13:
         R.ref_bilateral_texture_filter(img.ctypes.data, d.ctypes.data, w, h, 5, 2)
         assert np.array_equal(d, O.o_btf(img, 5, 2, O.ARITH_CPU))
+
+
+# ------------------------------------------------------------------ BASELINE configs[0]: lenna.png through the reference CPU path
+LENNA = np.load(os.path.join(os.path.dirname(__file__), "golden", "lenna_vectors.npz"))
+
+
+def test_lenna_bf_r5_cpu_mode_bit_exact():
+    """configs[0]: the restatement reproduces the reference's C++ CPU path on lenna.png bit for bit."""
+    img = LENNA["lenna_bgr"]
+    assert img.shape == (512, 512, 3)
+    assert np.array_equal(O.o_bf(img, 11, 10.0, 30.0, O.ARITH_CPU), LENNA["bf_r5_cpu"])
+
+
+def test_lenna_crop_abf_btf_cpu_mode_bit_exact():
+    crop = np.ascontiguousarray(LENNA["lenna_bgr"][128:384, 128:384])
+    assert np.array_equal(O.o_abf(crop, 15, 10.0, 30.0, O.ARITH_CPU), LENNA["abf_r7_crop_cpu"])
+    assert np.array_equal(O.o_btf(crop, 9, 3, O.ARITH_CPU), LENNA["btf_k9_n3_crop_cpu"])
