@@ -143,6 +143,16 @@ VIP_API int vip_gradient_f32(const float* d_src, float* d_dst, int width, int he
 VIP_API int vip_gradient_u8_strip(const uint8_t* d_src, float* d_dst, int width, int height, int channels,
                                   const vip_strip* strip, void* stream);
 
+/* ---- host-I/O edge: layout conversion ------------------------------------------------------------------
+ * vip_convert_to_bgr_u8: device twin of convert_to_3ch (sample/benchmark/main.cpp:91-103): src_channels 1 (GRAY2BGR:
+ * the channel is replicated), 3 (copy) or 4 (BGRA2BGR: alpha dropped) -> packed 3-channel.  swap_rb != 0 also swaps
+ * channels 0 and 2 (a PNG / PPM decoder delivers RGB(A), the filters' convention -- cv::imread -- is BGR).
+ * vip_scale_to_u8_f32: dst = saturate_u8(round_half_even(src * 255 / max_value)), the convert_to_u8 of
+ * sample/gradient/main.cpp:9-18 used to write a gradient magnitude as an 8-bit image. */
+VIP_API int vip_convert_to_bgr_u8(const uint8_t* d_src, int src_channels, uint8_t* d_dst, int width, int height,
+                                  int swap_rb, void* stream);
+VIP_API int vip_scale_to_u8_f32(const float* d_src, uint8_t* d_dst, size_t n, float max_value, void* stream);
+
 /* ---- border-replicated integral image -----------------------------------------------------------------
  * GPU twin of BorderReplicatedIntegralImage<uint8_t,3> (include/cpp/border_replicated_integral_image.hpp:6-85;
  * the reference has this on the CPU only).  The table is (height+2r+1) x (width+2r+1) x 3 uint32, row 0 and
@@ -159,6 +169,19 @@ VIP_API size_t vip_integral_table_elems(int width, int height, int radius);
  * quantity include/cpp/adaptive_bilateral_filter.hpp:53-57 reads from the table. */
 VIP_API int vip_integral_box_mean_u8c3(const uint32_t* d_table, float* d_mean, int width, int height, int radius,
                                        void* stream);
+
+/* Any source type / channel count of the reference template (BorderReplicatedIntegralImage<SrcType, Channels>,
+ * instantiated by its tests for uint8_t / uint16_t / float x 1..3 channels,
+ * test/border_replicated_integral_image.cpp:63-95).  src_type VIP_SRC_U8 / VIP_SRC_U16: uint32 table (modulo 2^32);
+ * VIP_SRC_F32: float table.  channels 1..4.  The table has (height+2r+1) x (width+2r+1) x channels elements.
+ * vip_integral_get: n rectangles (x0,y0,x1,y1) -> n x channels sums (uint32 or float like the table). */
+#define VIP_SRC_U8 0
+#define VIP_SRC_U16 1
+#define VIP_SRC_F32 2
+VIP_API int vip_integral_build(const void* d_src, void* d_table, int width, int height, int channels, int radius,
+                               int src_type, void* stream);
+VIP_API int vip_integral_get(const void* d_table, int width, int height, int channels, int radius, int src_type,
+                             const int32_t* d_rects, int n, void* d_out, void* stream);
 
 /* ---- bilateral texture filter -------------------------------------------------------------------------
  * replaces CudaBilateralTextureFilter (include/cuda/bilateral_texture_filter.hpp:7-17):

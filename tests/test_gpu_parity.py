@@ -279,6 +279,39 @@ def test_btf_end_to_end(vip, w, h, k, nitr):
         assert (d > 1).mean() < 0.02, f"{(d > 1).mean():.4f} of samples differ by more than 1 LSB from the CPU reference"
 
 
+# ------------------------------------------------------------------ host-I/O edge (sample/benchmark/main.cpp:91-103)
+@pytest.mark.parametrize("w,h", [(1, 1), (7, 3), (64, 64), (1921, 1079)])
+@pytest.mark.parametrize("ch,swap", [(1, False), (3, False), (3, True), (4, False), (4, True)])
+def test_convert_to_bgr(vip, w, h, ch, swap):
+    src = np.random.RandomState(w * ch).randint(0, 256, size=(h, w, ch)).astype(np.uint8)
+    d = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    vip.convert_to_bgr(dev(src), ch, d, w, h, swap)
+    torch.cuda.synchronize()
+    if ch == 1:
+        want = np.repeat(src, 3, axis=2)                 # cv::COLOR_GRAY2BGR
+    else:
+        want = src[..., :3]                              # cv::COLOR_BGRA2BGR / copy
+        if swap:
+            want = want[..., ::-1]
+    assert np.array_equal(d.cpu().numpy(), want)
+
+
+def test_convert_unaligned_and_scale_to_u8(vip):
+    w, h = 33, 5
+    buf = torch.from_numpy(np.random.RandomState(1).randint(0, 256, size=h * w * 4 + 1).astype(np.uint8)).cuda()
+    d = torch.empty((h * w * 3 + 1,), dtype=torch.uint8, device="cuda")
+    vip.convert_to_bgr(buf[1:], 4, d[1:], w, h, True)    # both pointers odd
+    torch.cuda.synchronize()
+    want = buf[1:].cpu().numpy().reshape(h, w, 4)[..., 2::-1]
+    assert np.array_equal(d[1:].cpu().numpy().reshape(h, w, 3), want)
+    g = (O.mt_f32(1000) * np.float32(1.7)).astype(np.float32)
+    out = torch.empty((1000,), dtype=torch.uint8, device="cuda")
+    vip.scale_to_u8(dev(g), out, 1000, float(g.max()))
+    torch.cuda.synchronize()
+    want = np.clip(np.rint((g * np.float32(255.0)) / np.float32(g.max())), 0, 255).astype(np.uint8)
+    assert np.array_equal(out.cpu().numpy(), want)
+
+
 # ------------------------------------------------------------------ integral image
 @pytest.mark.parametrize("r", [1, 3, 5])
 def test_integral_all_rectangles_5x5(vip, r):
@@ -291,6 +324,63 @@ def test_integral_all_rectangles_5x5(vip, r):
     torch.cuda.synchronize()
     assert np.array_equal(out.cpu().numpy(), sums)
     assert np.array_equal(ii.download_table().reshape(5 + 2 * r + 1, 5 + 2 * r + 1, 3), O.o_integral(src, r))
+
+
+def np_padded_integral(src, r, acc):
+    """include/cpp/border_replicated_integral_image.hpp:51-78 in numpy: clamp-pad, zero first row/column, 2-D prefix."""
+    h, w, c = src.shape
+    ys = np.clip(np.arange(-r, h + r), 0, h - 1)
+    xs = np.clip(np.arange(-r, w + r), 0, w - 1)
+    t = np.zeros((h + 2 * r + 1, w + 2 * r + 1, c), acc)
+    t[1:, 1:] = src[ys][:, xs]
+    return t.cumsum(0, dtype=acc).cumsum(1, dtype=acc)
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32])
+@pytest.mark.parametrize("ch", [1, 2, 3, 4])
+@pytest.mark.parametrize("r", [1, 3, 5])
+def test_integral_typed_all_rectangles_5x5(vip, dtype, ch, r):
+    """The reference's typed test (test/border_replicated_integral_image.cpp:6-95): every rectangle of a 5x5 image;
+    integers exact, float within 1 % (the reference's own tolerance, :36-39)."""
+    w = h = 5
+    if dtype == np.float32:
+        src = O.mt_f32(w * h * ch).reshape(h, w, ch)
+    else:
+        src = (np.random.RandomState(42).randint(0, 2**32, size=w * h * ch, dtype=np.uint64) % 255).astype(dtype).reshape(h, w, ch)
+    ii = vip.CudaBorderReplicatedIntegralImage(w, h, r, ch, dtype)
+    ii.build(dev(src))
+    rects = np.asarray([(x0, y0, x1, y1) for y0 in range(-r, h + r) for x0 in range(-r, w + r)
+                        for y1 in range(y0, h + r) for x1 in range(x0, w + r)], np.int32)
+    out = torch.empty((len(rects), ch), dtype=torch.float32 if dtype == np.float32 else torch.int32, device="cuda")
+    ii.get(dev(rects), len(rects), out)
+    torch.cuda.synchronize()
+    pad = np_padded_integral(src.astype(np.float64 if dtype == np.float32 else np.int64), r, np.float64 if dtype == np.float32 else np.int64)
+    x0, y0, x1, y1 = rects.T
+    want = pad[y1 + r + 1, x1 + r + 1] - pad[y1 + r + 1, x0 + r] - pad[y0 + r, x1 + r + 1] + pad[y0 + r, x0 + r]
+    got = out.cpu().numpy()
+    if dtype == np.float32:
+        assert np.all(np.abs(got - want) <= 1e-2 * np.abs(want) + 1e-3)
+    else:
+        assert np.array_equal(got.astype(np.int64), want)
+
+
+@pytest.mark.parametrize("dtype,ch,w,h,r", [(np.uint8, 1, 700, 300, 7), (np.uint16, 3, 513, 130, 4), (np.float32, 3, 300, 257, 5),
+                                            (np.uint8, 4, 1031, 67, 9), (np.uint8, 3, 3840, 2160, 7)])
+def test_integral_typed_tables(vip, dtype, ch, w, h, r):
+    rs = np.random.RandomState(w + ch)
+    src = rs.randint(0, 60000 if dtype == np.uint16 else 256, size=(h, w, ch)).astype(dtype)
+    if dtype == np.float32:
+        src = (src * np.float32(0.37)).astype(np.float32)
+    ii = vip.CudaBorderReplicatedIntegralImage(w, h, r, ch, dtype)
+    ii.build(dev(src))
+    torch.cuda.synchronize()
+    got = ii.download_table().reshape(h + 2 * r + 1, w + 2 * r + 1, ch)
+    if dtype == np.float32:
+        want = np_padded_integral(src.astype(np.float64), r, np.float64)
+        assert np.all(np.abs(got - want) <= 1e-4 * np.abs(want) + 1e-2)
+    else:
+        want = np_padded_integral(src.astype(np.uint64), r, np.uint64)
+        assert np.array_equal(got, (want & 0xFFFFFFFF).astype(np.uint32))     # modulo 2^32
 
 
 @pytest.mark.parametrize("w,h,r", [(300, 130, 7), (1000, 70, 4), (64, 64, 0), (513, 257, 15)])

@@ -7,12 +7,13 @@ Python mirror of the reference's host interface.  There is no CPU fallback.
 from . import capi
 from .capi import Strip, VipError, launch_count
 from .strips import StripPlan, halo_rows, plan_strips, to_strip
-from .filters import (CudaAdaptiveBilateralFilter, CudaBilateralFilter, CudaBilateralTextureFilter, CudaIntegralImage,
-                      DeviceImage, MultiGpuFilter, PinnedBuffer, cuda_gradient, cuda_gradient_strip,
+from .filters import (CudaAdaptiveBilateralFilter, CudaBilateralFilter, CudaBilateralTextureFilter, CudaBorderReplicatedIntegralImage,
+                      CudaIntegralImage,
+                      DeviceImage, MultiGpuFilter, PinnedBuffer, convert_to_bgr, cuda_gradient, cuda_gradient_strip, scale_to_u8,
                       device_synchronize)
 
 __all__ = [
     "capi", "Strip", "VipError", "launch_count", "CudaAdaptiveBilateralFilter", "CudaBilateralFilter",
-    "CudaBilateralTextureFilter", "CudaIntegralImage", "DeviceImage", "MultiGpuFilter", "PinnedBuffer",
-    "cuda_gradient", "cuda_gradient_strip", "device_synchronize", "StripPlan", "halo_rows", "plan_strips", "to_strip",
+    "CudaBilateralTextureFilter", "CudaBorderReplicatedIntegralImage", "CudaIntegralImage", "DeviceImage", "MultiGpuFilter", "PinnedBuffer",
+    "convert_to_bgr", "scale_to_u8", "cuda_gradient", "cuda_gradient_strip", "device_synchronize", "StripPlan", "halo_rows", "plan_strips", "to_strip",
 ]

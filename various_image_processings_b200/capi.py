@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("VIP_B200_LIB") or os.path.join(_HERE, "lib", "libvip_
 VIP_OK = 0
 VIP_LUT_CUDA, VIP_LUT_CPU = 0, 1
 VIP_MG_BF, VIP_MG_ABF, VIP_MG_BTF = 0, 1, 2
+VIP_SRC_U8, VIP_SRC_U16, VIP_SRC_F32 = 0, 1, 2
 
 
 class VipError(RuntimeError):
@@ -66,9 +67,13 @@ SIGNATURES = {
     "vip_gradient_u8": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "vip_gradient_f32": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "vip_gradient_u8_strip": (_i, [_vp, _vp, _i, _i, _i, C.POINTER(Strip), _vp]),
+    "vip_convert_to_bgr_u8": (_i, [_vp, _i, _vp, _i, _i, _i, _vp]),
+    "vip_scale_to_u8_f32": (_i, [_vp, _vp, _sz, _f, _vp]),
     "vip_integral_u8c3": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "vip_integral_get_u8c3": (_i, [_vp, _i, _i, _i, _vp, _i, _vp, _vp]),
     "vip_integral_table_elems": (_sz, [_i, _i, _i]),
+    "vip_integral_build": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "vip_integral_get": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp]),
     "vip_integral_box_mean_u8c3": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "vip_btf_create": (_i, [_pp, _i, _i, _i, _i]),
     "vip_btf_destroy": (_i, [_vp]),

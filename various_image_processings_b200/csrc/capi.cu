@@ -366,6 +366,21 @@ int vip_gradient_u8_strip(const uint8_t* d_src, float* d_dst, int width, int hei
                                       s->out_y0, s->out_rows, static_cast<cudaStream_t>(stream)));
 }
 
+/* ---------------------------------------------------------------- host-I/O edge: layout conversion */
+int vip_convert_to_bgr_u8(const uint8_t* d_src, int src_channels, uint8_t* d_dst, int width, int height, int swap_rb,
+                          void* stream) {
+    if (!d_src || !d_dst) return VIP_E_NULL;
+    if (width <= 0 || height <= 0) return VIP_E_SIZE;
+    if (src_channels != 1 && src_channels != 3 && src_channels != 4) return VIP_E_UNSUPPORTED;
+    return cu(vip::launch_convert_to_bgr(d_src, src_channels, d_dst, width, height, swap_rb,
+                                         static_cast<cudaStream_t>(stream)));
+}
+int vip_scale_to_u8_f32(const float* d_src, uint8_t* d_dst, size_t n, float max_value, void* stream) {
+    if (!d_src || !d_dst) return VIP_E_NULL;
+    if (!(max_value > 0.f)) return VIP_E_SIGMA;
+    return cu(vip::launch_scale_to_u8(d_src, d_dst, n, max_value, static_cast<cudaStream_t>(stream)));
+}
+
 /* ---------------------------------------------------------------- integral image */
 size_t vip_integral_table_elems(int width, int height, int radius) {
     if (width <= 0 || height <= 0 || radius < 0) return 0;
@@ -388,6 +403,23 @@ int vip_integral_box_mean_u8c3(const uint32_t* d_table, float* d_mean, int width
     if (!d_table || !d_mean) return VIP_E_NULL;
     if (width <= 0 || height <= 0 || radius < 0) return VIP_E_SIZE;
     return cu(vip::launch_integral_box_mean(d_table, d_mean, width, height, radius, static_cast<cudaStream_t>(stream)));
+}
+
+int vip_integral_build(const void* d_src, void* d_table, int width, int height, int channels, int radius, int src_type,
+                       void* stream) {
+    if (!d_src || !d_table) return VIP_E_NULL;
+    if (width <= 0 || height <= 0 || radius < 0 || channels < 1 || channels > 4) return VIP_E_SIZE;
+    if (src_type != VIP_SRC_U8 && src_type != VIP_SRC_U16 && src_type != VIP_SRC_F32) return VIP_E_UNSUPPORTED;
+    return cu(vip::launch_integral_any(d_src, d_table, width, height, channels, radius, src_type,
+                                       static_cast<cudaStream_t>(stream)));
+}
+int vip_integral_get(const void* d_table, int width, int height, int channels, int radius, int src_type,
+                     const int32_t* d_rects, int n, void* d_out, void* stream) {
+    if (!d_table || !d_rects || !d_out) return VIP_E_NULL;
+    if (width <= 0 || height <= 0 || radius < 0 || n < 0 || channels < 1 || channels > 4) return VIP_E_SIZE;
+    if (src_type != VIP_SRC_U8 && src_type != VIP_SRC_U16 && src_type != VIP_SRC_F32) return VIP_E_UNSUPPORTED;
+    return cu(vip::launch_integral_get_any(d_table, width, height, channels, radius, src_type == VIP_SRC_F32, d_rects, n,
+                                           d_out, static_cast<cudaStream_t>(stream)));
 }
 
 /* ---------------------------------------------------------------- BTF */

@@ -1,19 +1,26 @@
 // Border-replicated integral image on the GPU (sm_100a).  GPU twin of the reference's CPU-only
-// BorderReplicatedIntegralImage<uint8_t,3> (include/cpp/border_replicated_integral_image.hpp:6-85): a
-// (H+2r+1) x (W+2r+1) x 3 table over the clamp-padded image, first row / column zero; get(x0,y0,x1,y1) is the
-// inclusive box sum from four corners (:34-47).  All sums are uint32 modulo 2^32: differences of corners are
-// exact for any image size (the reference's int32 table overflows -- UB -- beyond ~4K).
+// BorderReplicatedIntegralImage<SrcType, Channels> (include/cpp/border_replicated_integral_image.hpp:6-85): a
+// (H+2r+1) x (W+2r+1) x C table over the clamp-padded image, first row / column zero; get(x0,y0,x1,y1) is the
+// inclusive box sum from four corners (:34-47).  Integer sources (u8, u16) accumulate in uint32 modulo 2^32:
+// differences of corners are exact for any image size (the reference's int32 table overflows -- UB -- beyond ~4K,
+// SURVEY.md 8a/a11).  Float sources accumulate in fp32 (the reference's own test allows 1 % there,
+// test/border_replicated_integral_image.cpp:36-39).
 //
-//  K1 row pass    one CTA per padded row; 256-pixel chunks are scanned with warp shuffles (__shfl_up_sync
-//                 inclusive scan inside each warp, one shared-memory hop across the 8 warps) and a running carry,
-//                 reading the clamped source row once and writing coalesced 12-byte records;
-//  K2 column pass 64-row bands, one thread per (column, channel): band-local running sums, band totals to a
-//                 small aux array;
-//  K3 band fix-up adds the exclusive prefix of the band totals.
-// Traffic: 3 B read + 12 B written (K1) + 24 B (K2) + 24 B (K3) per padded cell.
+// The stage is HBM-bound: 12 B written + C bytes read per padded cell is the floor.  Three launches:
+//  K1 band sums   32-row bands x 256-column chunks, one thread per padded column: vertical sums of the clamped source,
+//                 written at every 8th row (the running sum inside the band) plus the band total;
+//  K2 band scan   exclusive prefix of the band totals over the bands (tiny: th/32 entries per column);
+//  K3 scan+store  one CTA per 8-row band walks along the row in 256-column chunks.  Phase A: a thread per column
+//                 turns the 8 source rows into vertical prefix sums (start value from K1/K2) in shared memory;
+//                 phase B: a WARP per row, a lane per 8 adjacent columns: lane-local prefix, then one
+//                 __shfl_up_sync inclusive scan of the lane totals and a register carry along the row -- no block
+//                 barrier inside the scan; phase C: fully coalesced 128-byte stores of the finished chunk.
+// Traffic: the source is read twice (the second time from L2 for anything up to 8K), the table written once; the
+// K1/K2 arrays are 1/8 of the table and stay in L2.
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <mutex>
 
 #include "vip_internal.h"
 
@@ -23,104 +30,280 @@ namespace {
 __device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
 constexpr int kScanThreads = 256;
-constexpr int kBandRows = 64;
+constexpr int kChunk = 256;     // padded columns per chunk
+constexpr int kSubRows = 8;     // rows of a K3 band (= warps per CTA)
+constexpr int kBandRows = 32;   // rows of a K1/K2 band
+constexpr int kSubPerBand = kBandRows / kSubRows;
 
-__global__ void __launch_bounds__(kScanThreads) integral_rows_kernel(const std::uint8_t* __restrict__ src,
-                                                                    std::uint32_t* __restrict__ table, const int W,
-                                                                    const int H, const int r) {
-    const int tw = W + 2 * r + 1;
-    const int Y = blockIdx.x;  // padded row, 0 .. H+2r
-    std::uint32_t* trow = table + static_cast<size_t>(Y) * tw * 3;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (Y == 0) {
-        for (int i = tid; i < tw * 3; i += kScanThreads) trow[i] = 0u;
-        return;
-    }
-    const std::uint8_t* srow = src + static_cast<size_t>(clampi(Y - 1 - r, 0, H - 1)) * W * 3;
-    __shared__ std::uint32_t warp_tot[3][kScanThreads / 32];
-    __shared__ std::uint32_t carry_s[3];
-    if (tid < 3) {
-        carry_s[tid] = 0u;
-        trow[tid] = 0u;  // column 0
-    }
-    __syncthreads();
-    for (int X0 = 1; X0 < tw; X0 += kScanThreads) {
-        const int X = X0 + tid;
-        std::uint32_t v0 = 0, v1 = 0, v2 = 0;
-        if (X < tw) {
-            const std::uint8_t* p = srow + clampi(X - 1 - r, 0, W - 1) * 3;
-            v0 = __ldg(p);
-            v1 = __ldg(p + 1);
-            v2 = __ldg(p + 2);
-        }
+template <typename S>
+struct AccOf {
+    using type = std::uint32_t;
+};
+template <>
+struct AccOf<float> {
+    using type = float;
+};
+
+// value of padded cell (Y, X): 0 on the first row / column, else the clamped source pixel
+template <typename S, int C>
+__device__ __forceinline__ const S* cell_ptr(const S* __restrict__ src, const int W, const int H, const int r,
+                                             const int Y, const int X) {
+    const int sy = clampi(Y - 1 - r, 0, H - 1), sx = clampi(X - 1 - r, 0, W - 1);
+    return src + (static_cast<size_t>(sy) * W + sx) * C;
+}
+
+// K1: sub[(Y/8)][X][c] = sum of padded rows [32*band, Y) of column X (Y a multiple of 8); tot[band][X][c] = band total
+template <typename S, int C>
+__global__ void __launch_bounds__(kScanThreads) integral_bands_kernel(const S* __restrict__ src,
+                                                                     typename AccOf<S>::type* __restrict__ sub,
+                                                                     typename AccOf<S>::type* __restrict__ tot,
+                                                                     const int W, const int H, const int r) {
+    using A = typename AccOf<S>::type;
+    const int tw = W + 2 * r + 1, th = H + 2 * r + 1;
+    const int X = blockIdx.x * kScanThreads + threadIdx.x;
+    if (X >= tw) return;
+    const int band = blockIdx.y;
+    const int Y0 = band * kBandRows;
+    A acc[C];
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const std::uint32_t a0 = __shfl_up_sync(0xffffffffu, v0, d);
-            const std::uint32_t a1 = __shfl_up_sync(0xffffffffu, v1, d);
-            const std::uint32_t a2 = __shfl_up_sync(0xffffffffu, v2, d);
-            if (lane >= d) {
-                v0 += a0;
-                v1 += a1;
-                v2 += a2;
+    for (int c = 0; c < C; ++c) acc[c] = A(0);
+#pragma unroll
+    for (int q = 0; q < kSubPerBand; ++q) {
+        const int Ys = Y0 + q * kSubRows;
+        if (Ys >= th) break;
+        A* o = sub + (static_cast<size_t>(Ys / kSubRows) * tw + X) * C;
+#pragma unroll
+        for (int c = 0; c < C; ++c) o[c] = acc[c];
+#pragma unroll
+        for (int j = 0; j < kSubRows; ++j) {
+            const int Y = Ys + j;
+            if (Y >= 1 && Y < th && X >= 1) {
+                const S* p = cell_ptr<S, C>(src, W, H, r, Y, X);
+#pragma unroll
+                for (int c = 0; c < C; ++c) acc[c] += static_cast<A>(__ldg(p + c));
             }
         }
-        if (lane == 31) {
-            warp_tot[0][warp] = v0;
-            warp_tot[1][warp] = v1;
-            warp_tot[2][warp] = v2;
+    }
+    A* t = tot + (static_cast<size_t>(band) * tw + X) * C;
+#pragma unroll
+    for (int c = 0; c < C; ++c) t[c] = acc[c];
+}
+
+// K2: in-place exclusive scan of tot over the bands.  A CTA owns 32 (column, channel) entries; its 8 warps split the
+// bands into 8 contiguous segments (all loads of a segment are independent, so the kernel costs about two memory
+// latencies instead of nbands of them), exchange the segment totals through shared memory and write the prefixes.
+constexpr int kScanSeg = 8;
+template <typename A>
+__global__ void __launch_bounds__(kScanThreads) integral_band_scan_kernel(A* __restrict__ tot, const int pitch,
+                                                                         const int nbands) {
+    __shared__ A seg_tot[kScanSeg][32];
+    const int lane = threadIdx.x & 31, seg = threadIdx.x >> 5;
+    const int i = blockIdx.x * 32 + lane;
+    const int per = (nbands + kScanSeg - 1) / kScanSeg;
+    const int b0 = min(seg * per, nbands), b1 = min(b0 + per, nbands);
+    constexpr int kKeep = 24;  // bands of a segment kept in registers (nbands <= 192 <=> image height <= ~6100 rows)
+    A v[kKeep];
+    A sum = A(0);
+    if (i < pitch) {
+#pragma unroll
+        for (int j = 0; j < kKeep; ++j) v[j] = (b0 + j < b1) ? tot[static_cast<size_t>(b0 + j) * pitch + i] : A(0);
+#pragma unroll
+        for (int j = 0; j < kKeep; ++j) sum += v[j];
+        for (int b = b0 + kKeep; b < b1; ++b) sum += tot[static_cast<size_t>(b) * pitch + i];
+    }
+    seg_tot[seg][lane] = sum;
+    __syncthreads();
+    if (i >= pitch) return;
+    A run = A(0);
+    for (int q = 0; q < seg; ++q) run += seg_tot[q][lane];
+#pragma unroll
+    for (int j = 0; j < kKeep; ++j) {
+        if (b0 + j < b1) {
+            tot[static_cast<size_t>(b0 + j) * pitch + i] = run;
+            run += v[j];
+        }
+    }
+    for (int b = b0 + kKeep; b < b1; ++b) {
+        const A x = tot[static_cast<size_t>(b) * pitch + i];
+        tot[static_cast<size_t>(b) * pitch + i] = run;
+        run += x;
+    }
+}
+
+// K3: scan + store (see the header).  S holds the chunk as [row][pad(column*C + channel)], one spare word after every
+// 8*C so that the 32 lanes of phase B start in 32 different banks.
+template <typename S, int C>
+__global__ void __launch_bounds__(kScanThreads) integral_scan_kernel(const S* __restrict__ src,
+                                                                    const typename AccOf<S>::type* __restrict__ sub,
+                                                                    const typename AccOf<S>::type* __restrict__ tot,
+                                                                    typename AccOf<S>::type* __restrict__ table,
+                                                                    const int W, const int H, const int r) {
+    using A = typename AccOf<S>::type;
+    constexpr int kLaneWords = 8 * C;               // words one lane owns in phase B
+    constexpr int kRowWords = kChunk * C + kChunk / 8;
+    __shared__ A Sm[kSubRows][kRowWords];
+    const int tw = W + 2 * r + 1, th = H + 2 * r + 1;
+    const int b8 = blockIdx.x, Y0 = b8 * kSubRows;
+    const int band = Y0 / kBandRows;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    S pix[kSubRows][C];
+    A start[C];
+    auto prefetch = [&](const int X0) {
+        const int X = X0 + tid;
+        const bool in = X >= 1 && X < tw;
+#pragma unroll
+        for (int c = 0; c < C; ++c) start[c] = A(0);
+        if (in) {
+            const A* t = tot + (static_cast<size_t>(band) * tw + X) * C;
+            const A* u = sub + (static_cast<size_t>(b8) * tw + X) * C;
+#pragma unroll
+            for (int c = 0; c < C; ++c) start[c] = __ldg(t + c) + __ldg(u + c);
+        }
+        const S* const colp = src + static_cast<size_t>(clampi(X - 1 - r, 0, W - 1)) * C;
+#pragma unroll
+        for (int j = 0; j < kSubRows; ++j) {
+            const int Y = Y0 + j;
+            const bool ok = in && Y >= 1 && Y < th;
+            const S* p = colp + static_cast<size_t>(clampi(Y - 1 - r, 0, H - 1)) * W * C;
+#pragma unroll
+            for (int c = 0; c < C; ++c) pix[j][c] = ok ? __ldg(p + c) : S(0);
+        }
+    };
+
+    A carry[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) carry[c] = A(0);
+    prefetch(0);
+    for (int X0 = 0; X0 < tw; X0 += kChunk) {
+        // phase A: vertical prefix of this thread's column
+        {
+            A acc[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) acc[c] = start[c];
+            const int w0 = tid * C + tid / 8;
+#pragma unroll
+            for (int j = 0; j < kSubRows; ++j) {
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    acc[c] += static_cast<A>(pix[j][c]);
+                    Sm[j][w0 + c] = acc[c];
+                }
+            }
         }
         __syncthreads();
-        std::uint32_t o0 = carry_s[0], o1 = carry_s[1], o2 = carry_s[2];
-        for (int w = 0; w < warp; ++w) {
-            o0 += warp_tot[0][w];
-            o1 += warp_tot[1][w];
-            o2 += warp_tot[2][w];
-        }
-        v0 += o0;
-        v1 += o1;
-        v2 += o2;
-        if (X < tw) {
-            trow[X * 3 + 0] = v0;
-            trow[X * 3 + 1] = v1;
-            trow[X * 3 + 2] = v2;
+        if (X0 + kChunk < tw) prefetch(X0 + kChunk);  // in flight during phases B and C
+        // phase B: warp = row, lane = 8 adjacent columns
+        {
+            A* row = &Sm[warp][lane * (kLaneWords + 1)];
+            A v[8][C], run[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) run[c] = A(0);
+#pragma unroll
+            for (int m = 0; m < 8; ++m) {
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    run[c] += row[m * C + c];
+                    v[m][c] = run[c];
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                A incl = run[c];
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const A up = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += up;
+                }
+                A excl = __shfl_up_sync(0xffffffffu, incl, 1);
+                if (lane == 0) excl = A(0);
+                excl += carry[c];
+                carry[c] += __shfl_sync(0xffffffffu, incl, 31);
+#pragma unroll
+                for (int m = 0; m < 8; ++m) row[m * C + c] = v[m][c] + excl;
+            }
         }
         __syncthreads();
-        if (tid == kScanThreads - 1) {
-            carry_s[0] = v0;
-            carry_s[1] = v1;
-            carry_s[2] = v2;
+        // phase C: coalesced stores
+        {
+            const int nwords = min(kChunk, tw - X0) * C;
+            const int nrows = min(kSubRows, th - Y0);
+            A* const tbase = table + (static_cast<size_t>(Y0) * tw + X0) * C;
+#pragma unroll
+            for (int q = 0; q < C; ++q) {
+                const int i = tid + q * kScanThreads;
+                if (i < nwords) {
+                    const int si = i + i / kLaneWords;
+#pragma unroll
+                    for (int j = 0; j < kSubRows; ++j)
+                        if (j < nrows) tbase[static_cast<size_t>(j) * tw * C + i] = Sm[j][si];
+                }
+            }
         }
         __syncthreads();
     }
 }
 
-__global__ void __launch_bounds__(kScanThreads) integral_cols_kernel(std::uint32_t* __restrict__ table,
-                                                                    std::uint32_t* __restrict__ aux, const int pitch,
-                                                                    const int th) {
-    const int col = blockIdx.x * kScanThreads + threadIdx.x;  // column*3 + channel
-    if (col >= pitch) return;
-    const int band = blockIdx.y;
-    const int y0 = band * kBandRows, y1 = min(y0 + kBandRows, th);
-    std::uint32_t acc = 0;
-    std::uint32_t* p = table + static_cast<size_t>(y0) * pitch + col;
-    for (int y = y0; y < y1; ++y, p += pitch) {
-        acc += *p;
-        *p = acc;
+// Stream-ordered scratch from a library-private memory pool that keeps its memory between calls (the default pool
+// gives freed blocks back to the driver at the next synchronisation; re-acquiring ~16 MB per call cost more than the
+// three kernels together).
+cudaError_t scratch_alloc(void** p, size_t bytes, cudaStream_t stream) {
+    static std::mutex mu;
+    static cudaMemPool_t pools[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaMallocAsync(p, bytes, stream);
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!pools[dev]) {
+            cudaMemPoolProps props = {};
+            props.allocType = cudaMemAllocationTypePinned;
+            props.handleTypes = cudaMemHandleTypeNone;
+            props.location.type = cudaMemLocationTypeDevice;
+            props.location.id = dev;
+            e = cudaMemPoolCreate(&pools[dev], &props);
+            if (e != cudaSuccess) return e;
+            unsigned long long keep = ~0ull;
+            cudaMemPoolSetAttribute(pools[dev], cudaMemPoolAttrReleaseThreshold, &keep);
+        }
     }
-    aux[static_cast<size_t>(band) * pitch + col] = acc;
+    return cudaMallocFromPoolAsync(p, bytes, pools[dev], stream);
 }
 
-__global__ void __launch_bounds__(kScanThreads) integral_fix_kernel(std::uint32_t* __restrict__ table,
-                                                                   const std::uint32_t* __restrict__ aux,
-                                                                   const int pitch, const int th) {
-    const int col = blockIdx.x * kScanThreads + threadIdx.x;
-    if (col >= pitch) return;
-    const int band = blockIdx.y + 1;
-    std::uint32_t off = 0;
-    for (int b = 0; b < band; ++b) off += __ldg(aux + static_cast<size_t>(b) * pitch + col);
-    const int y0 = band * kBandRows, y1 = min(y0 + kBandRows, th);
-    std::uint32_t* p = table + static_cast<size_t>(y0) * pitch + col;
-    for (int y = y0; y < y1; ++y, p += pitch) *p += off;
+template <typename S, int C>
+cudaError_t launch_integral_t(const S* src, typename AccOf<S>::type* table, int width, int height, int radius,
+                              cudaStream_t stream) {
+    using A = typename AccOf<S>::type;
+    const int tw = width + 2 * radius + 1, th = height + 2 * radius + 1;
+    const int nsub = (th + kSubRows - 1) / kSubRows, nbands = (th + kBandRows - 1) / kBandRows;
+    const size_t row_elems = static_cast<size_t>(tw) * C;
+    A* aux = nullptr;
+    cudaError_t e = scratch_alloc(reinterpret_cast<void**>(&aux), (nsub + nbands) * row_elems * sizeof(A), stream);
+    if (e != cudaSuccess) return e;
+    A* sub = aux;
+    A* tot = aux + nsub * row_elems;
+    const dim3 g1((tw + kScanThreads - 1) / kScanThreads, nbands);
+    integral_bands_kernel<S, C><<<g1, kScanThreads, 0, stream>>>(src, sub, tot, width, height, radius);
+    integral_band_scan_kernel<A><<<(static_cast<int>(row_elems) + 31) / 32, kScanThreads, 0, stream>>>(
+        tot, static_cast<int>(row_elems), nbands);
+    integral_scan_kernel<S, C><<<nsub, kScanThreads, 0, stream>>>(src, sub, tot, table, width, height, radius);
+    count_launch(3);
+    e = cudaGetLastError();
+    cudaFreeAsync(aux, stream);
+    return e;
+}
+
+template <typename S>
+cudaError_t launch_integral_c(const S* src, typename AccOf<S>::type* table, int width, int height, int channels,
+                              int radius, cudaStream_t stream) {
+    switch (channels) {
+        case 1: return launch_integral_t<S, 1>(src, table, width, height, radius, stream);
+        case 2: return launch_integral_t<S, 2>(src, table, width, height, radius, stream);
+        case 3: return launch_integral_t<S, 3>(src, table, width, height, radius, stream);
+        case 4: return launch_integral_t<S, 4>(src, table, width, height, radius, stream);
+        default: return cudaErrorInvalidValue;
+    }
 }
 
 __device__ __forceinline__ void box3(const std::uint32_t* __restrict__ table, const int tw, const int r, const int x0,
@@ -163,24 +346,49 @@ __global__ void integral_box_mean_kernel(const std::uint32_t* __restrict__ table
 
 cudaError_t launch_integral_u8c3(const std::uint8_t* src, std::uint32_t* table, int width, int height, int radius,
                                  cudaStream_t stream) {
-    const int tw = width + 2 * radius + 1, th = height + 2 * radius + 1;
-    const int pitch = tw * 3;
-    const int nbands = (th + kBandRows - 1) / kBandRows;
-    std::uint32_t* aux = nullptr;
-    cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&aux), static_cast<size_t>(nbands) * pitch * 4, stream);
-    if (e != cudaSuccess) return e;
-    integral_rows_kernel<<<th, kScanThreads, 0, stream>>>(src, table, width, height, radius);
-    const dim3 grid((pitch + kScanThreads - 1) / kScanThreads, nbands);
-    integral_cols_kernel<<<grid, kScanThreads, 0, stream>>>(table, aux, pitch, th);
-    count_launch(2);
-    if (nbands > 1) {
-        const dim3 grid2(grid.x, nbands - 1);
-        integral_fix_kernel<<<grid2, kScanThreads, 0, stream>>>(table, aux, pitch, th);
-        count_launch();
+    return launch_integral_t<std::uint8_t, 3>(src, table, width, height, radius, stream);
+}
+
+cudaError_t launch_integral_any(const void* src, void* table, int width, int height, int channels, int radius,
+                                int src_type, cudaStream_t stream) {
+    switch (src_type) {
+        case 0: return launch_integral_c(static_cast<const std::uint8_t*>(src), static_cast<std::uint32_t*>(table), width,
+                                         height, channels, radius, stream);
+        case 1: return launch_integral_c(static_cast<const std::uint16_t*>(src), static_cast<std::uint32_t*>(table), width,
+                                         height, channels, radius, stream);
+        case 2: return launch_integral_c(static_cast<const float*>(src), static_cast<float*>(table), width, height,
+                                         channels, radius, stream);
+        default: return cudaErrorInvalidValue;
     }
-    e = cudaGetLastError();
-    cudaFreeAsync(aux, stream);
-    return e;
+}
+
+// get() for any channel count / accumulator type: out is n x channels
+template <typename A>
+__global__ void integral_get_any_kernel(const A* __restrict__ table, const int W, const int C, const int r,
+                                        const std::int32_t* __restrict__ rects, const int n, A* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * C) return;
+    const int q = i / C, ch = i - q * C;
+    const int tw = W + 2 * r + 1;
+    const int x0 = rects[4 * q], y0 = rects[4 * q + 1], x1 = rects[4 * q + 2], y1 = rects[4 * q + 3];
+    auto at = [&](int Y, int X) { return __ldg(table + (static_cast<size_t>(Y) * tw + X) * C + ch); };
+    // include/cpp/border_replicated_integral_image.hpp:34-47, same left-to-right order (matters for float)
+    out[i] = at(y1 + r + 1, x1 + r + 1) - at(y1 + r + 1, x0 + r) - at(y0 + r, x1 + r + 1) + at(y0 + r, x0 + r);
+}
+
+cudaError_t launch_integral_get_any(const void* table, int width, int height, int channels, int radius, int is_float,
+                                    const std::int32_t* rects, int n, void* out, cudaStream_t stream) {
+    (void)height;
+    if (n <= 0) return cudaSuccess;
+    const int total = n * channels;
+    if (is_float)
+        integral_get_any_kernel<float><<<(total + 255) / 256, 256, 0, stream>>>(
+            static_cast<const float*>(table), width, channels, radius, rects, n, static_cast<float*>(out));
+    else
+        integral_get_any_kernel<std::uint32_t><<<(total + 255) / 256, 256, 0, stream>>>(
+            static_cast<const std::uint32_t*>(table), width, channels, radius, rects, n, static_cast<std::uint32_t*>(out));
+    count_launch();
+    return cudaGetLastError();
 }
 
 cudaError_t launch_integral_get(const std::uint32_t* table, int width, int height, int radius,

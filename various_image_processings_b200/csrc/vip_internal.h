@@ -53,10 +53,20 @@ cudaError_t launch_guide(const float* blurred, const float* rtv, std::uint8_t* g
 // integral.cu
 cudaError_t launch_integral_u8c3(const std::uint8_t* src, std::uint32_t* table, int width, int height, int radius,
                                  cudaStream_t stream);
+// src_type: 0 = u8, 1 = u16 (uint32 table), 2 = f32 (float table); channels 1..4
+cudaError_t launch_integral_any(const void* src, void* table, int width, int height, int channels, int radius,
+                                int src_type, cudaStream_t stream);
+cudaError_t launch_integral_get_any(const void* table, int width, int height, int channels, int radius, int is_float,
+                                    const std::int32_t* rects, int n, void* out, cudaStream_t stream);
 cudaError_t launch_integral_get(const std::uint32_t* table, int width, int height, int radius,
                                 const std::int32_t* rects, int n, std::uint32_t* out, cudaStream_t stream);
 cudaError_t launch_integral_box_mean(const std::uint32_t* table, float* mean, int width, int height, int radius,
                                      cudaStream_t stream);
+
+// convert.cu
+cudaError_t launch_convert_to_bgr(const std::uint8_t* src, int src_channels, std::uint8_t* dst, int width, int height,
+                                  int swap_rb, cudaStream_t stream);
+cudaError_t launch_scale_to_u8(const float* src, std::uint8_t* dst, size_t n, float max_value, cudaStream_t stream);
 
 void count_launch(int n = 1);
 

@@ -246,6 +246,17 @@ def cuda_gradient_strip(d_src, d_dst, width, height, src_ch, strip, stream=None)
           "vip_gradient_u8_strip")
 
 
+def convert_to_bgr(d_src, src_channels, d_dst, width, height, swap_rb=False, stream=None):
+    """Device twin of convert_to_3ch (sample/benchmark/main.cpp:91-103): gray / 3-channel / 4-channel -> packed BGR."""
+    check(lib().vip_convert_to_bgr_u8(_ptr(d_src), src_channels, _ptr(d_dst), width, height, int(bool(swap_rb)),
+                                      _stream(stream)), "vip_convert_to_bgr_u8")
+
+
+def scale_to_u8(d_src, d_dst, n, max_value, stream=None):
+    """convert_to_u8 of sample/gradient/main.cpp:9-18: round(src * 255 / max) saturated to uint8."""
+    check(lib().vip_scale_to_u8_f32(_ptr(d_src), _ptr(d_dst), n, float(max_value), _stream(stream)), "vip_scale_to_u8_f32")
+
+
 class CudaIntegralImage:
     """GPU twin of BorderReplicatedIntegralImage<uint8_t,3> (include/cpp/border_replicated_integral_image.hpp)."""
 
@@ -268,6 +279,36 @@ class CudaIntegralImage:
     def download_table(self):
         raw = self.table.download()
         return raw.view(np.uint32)
+
+
+class CudaBorderReplicatedIntegralImage:
+    """BorderReplicatedIntegralImage<SrcType, Channels> on the GPU for the source types / channel counts the reference
+    template is instantiated with (uint8, uint16, float32; 1..4 channels;
+    test/border_replicated_integral_image.cpp:63-95).  Integer tables are uint32 (modulo 2^32), float tables float32."""
+    SRC = {np.dtype(np.uint8): capi.VIP_SRC_U8, np.dtype(np.uint16): capi.VIP_SRC_U16, np.dtype(np.float32): capi.VIP_SRC_F32}
+
+    def __init__(self, width, height, radius, channels=3, dtype=np.uint8):
+        self.dtype = np.dtype(dtype)
+        if self.dtype not in self.SRC:
+            raise TypeError("integral image source must be uint8, uint16 or float32")
+        self.width, self.height, self.radius, self.channels = width, height, radius, channels
+        self.src_type = self.SRC[self.dtype]
+        self.table = DeviceImage(width + 2 * radius + 1, height + 2 * radius + 1, channels, np.float32)  # 4-byte cells
+
+    @property
+    def table_dtype(self):
+        return np.dtype(np.float32) if self.src_type == capi.VIP_SRC_F32 else np.dtype(np.uint32)
+
+    def build(self, d_src, stream=None):
+        check(lib().vip_integral_build(_ptr(d_src), self.table.get(), self.width, self.height, self.channels, self.radius,
+                                       self.src_type, _stream(stream)), "vip_integral_build")
+
+    def get(self, d_rects, n, d_out, stream=None):
+        check(lib().vip_integral_get(self.table.get(), self.width, self.height, self.channels, self.radius, self.src_type,
+                                     _ptr(d_rects), n, _ptr(d_out), _stream(stream)), "vip_integral_get")
+
+    def download_table(self):
+        return self.table.download().view(self.table_dtype)
 
 
 class MultiGpuFilter:
