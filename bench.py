@@ -43,6 +43,7 @@ WORKLOADS = {
     "bf_1080p": ("bf", 1920, 1080, 9, 0, "bilateral filter k=9 on 1080p frames (configs[4])"),
     "abf_1080p": ("abf", 1920, 1080, 9, 0, "adaptive bilateral filter k=9 on 1080p frames (configs[4])"),
     "btf_1080p": ("btf", 1920, 1080, 9, 3, "bilateral texture filter k=9 nitr=3 on 1080p frames (configs[4])"),
+    "stream_1080p": ("all", 1920, 1080, 9, 3, "1080p RGB frame stream through all three filters (BF k=9, ABF k=9, BTF k=9 x3), frames dealt to the GPUs (configs[4]; --steps = frames per GPU)"),
 }
 L2_BYTES = 126 * 1024 * 1024
 
@@ -115,23 +116,19 @@ def cpu_reference(filt, w, h, ksize, nitr, sample_rows, threads, repeats=1):
         kind = "reference"
         cores = threads or (os.cpu_count() or 1)
         R.ref_set_num_threads(cores)
-        if filt == "bf":
-            run = lambda: R.ref_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0)
-        elif filt == "abf":
-            run = lambda: R.ref_adaptive_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0)
-        else:
-            run = lambda: R.ref_bilateral_texture_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, nitr)
+        r_bf = lambda: R.ref_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0)
+        r_abf = lambda: R.ref_adaptive_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0)
+        r_btf = lambda: R.ref_bilateral_texture_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, nitr)
+        run = {"bf": r_bf, "abf": r_abf, "btf": r_btf, "all": lambda: (r_bf(), r_abf(), r_btf())}[filt]
     else:
         kind = "port"
         L = O.oracle()
         L.vipo_set_num_threads(threads or 0)
         cores = L.vipo_get_num_threads()
-        if filt == "bf":
-            run = lambda: L.vipo_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0, 1)
-        elif filt == "abf":
-            run = lambda: L.vipo_adaptive_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0, 1)
-        else:
-            run = lambda: L.vipo_bilateral_texture_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, nitr, 1)
+        r_bf = lambda: L.vipo_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0, 1)
+        r_abf = lambda: L.vipo_adaptive_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0, 1)
+        r_btf = lambda: L.vipo_bilateral_texture_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, nitr, 1)
+        run = {"bf": r_bf, "abf": r_abf, "btf": r_btf, "all": lambda: (r_bf(), r_abf(), r_btf())}[filt]
     best = float("inf")
     for _ in range(repeats):
         t0 = time.perf_counter()
@@ -143,7 +140,7 @@ def cpu_reference(filt, w, h, ksize, nitr, sample_rows, threads, repeats=1):
 
 
 def sample_rows_for(filt, w, h, ksize):
-    taps = ksize * ksize * (2 if filt == "abf" else 1) * (4 if filt == "btf" else 1)
+    taps = ksize * ksize * {"bf": 1, "abf": 2, "btf": 4, "all": 7}[filt]
     # ~1e9 tap evaluations per sample: about a second on a many-core host, bounded on a small one
     rows = int(1e9 / (taps * w))
     return max(4 * ksize, min(h, rows - rows % 8))
@@ -246,9 +243,20 @@ def main():
     elif filt == "abf":
         F = vip.CudaAdaptiveBilateralFilter(w, h, ksize)
         step = lambda i: F.execute_async(d_src[i % n_pool], d_dst[i % n_pool])
-    else:
+    elif filt == "btf":
         F = vip.CudaBilateralTextureFilter(w, h, ksize, nitr)
         step = lambda i: F.execute_async(d_src[i % n_pool], d_dst[i % n_pool])
+    else:
+        F = (vip.CudaBilateralFilter(w, h, ksize), vip.CudaAdaptiveBilateralFilter(w, h, ksize),
+             vip.CudaBilateralTextureFilter(w, h, ksize, nitr))
+        d_dst2 = [torch.empty_like(d) for d in d_dst]
+        d_dst3 = [torch.empty_like(d) for d in d_dst]
+
+        def step(i):
+            j = i % n_pool
+            F[0].bilateral_filter_async(d_src[j], d_dst[j])
+            F[1].execute_async(d_src[j], d_dst2[j])
+            F[2].execute_async(d_src[j], d_dst3[j])
 
     def barrier():
         if world > 1:
@@ -289,6 +297,10 @@ def main():
         slots.append((src_img, dst_img, hin, hout, torch.cuda.Stream()))
     if filt == "btf":
         F2 = [F, vip.CudaBilateralTextureFilter(w, h, ksize, nitr)]   # scratch is per object
+    n_out = 3 if filt == "all" else 1                                 # result images downloaded per step
+    if filt == "all":
+        F2 = [F[2], vip.CudaBilateralTextureFilter(w, h, ksize, nitr)]
+        extra = [[(vip.DeviceImage(w, out_rows, 3), vip.PinnedBuffer(w * out_rows * 3)) for _ in range(2)] for _ in range(2)]
 
     def e2e_step(i):
         src_img, dst_img, hin, hout, st = slots[i & 1]
@@ -300,8 +312,15 @@ def main():
                 F.bilateral_filter_async(src_img, dst_img, stream=st)
         elif filt == "abf":
             F.execute_async(src_img, dst_img, stream=st)
-        else:
+        elif filt == "btf":
             F2[i & 1].execute_async(src_img, dst_img, stream=st)
+        else:
+            (d2, h2), (d3, h3) = extra[i & 1]
+            F[0].bilateral_filter_async(src_img, dst_img, stream=st)
+            F[1].execute_async(src_img, d2, stream=st)
+            F2[i & 1].execute_async(src_img, d3, stream=st)
+            d2.download(h2.array, stream=st)
+            d3.download(h3.array, stream=st)
         dst_img.download(hout.array, stream=st)
 
     for i in range(2):
@@ -334,12 +353,12 @@ def main():
     peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
     local_pixels = w * out_rows
     kernels_per_step = launches / max(args.steps, 1)
-    taps = mask_taps(radius if filt != "btf" else ksize - 1)
-    if filt == "btf":
+    taps = mask_taps(radius if filt not in ("btf", "all") else ksize - 1)
+    if filt in ("btf", "all"):
         alg_bytes = local_pixels * 9.0                    # dominant kernel = joint bilateral: src + guide in, dst out
         kernel_ms = None                                  # several kernels per step: see profiles/ for the split
         instr_per_tap = 9.7
-        taps_per_px = taps * nitr
+        taps_per_px = taps * nitr + (2 * mask_taps(radius) if filt == "all" else 0)
     else:
         alg_bytes = local_pixels * 6.0                    # 3 B in + 3 B out per pixel
         kernel_ms = ms_step
@@ -351,7 +370,7 @@ def main():
     except (OSError, ValueError):
         pass
     roof = {"bound": "hbm", "unit": "GB/s", "peak": hbm_peak, "peak_source": peak_src, "traffic": traffic,
-            "kernel": {"bf": "stencil_kernel<BF>", "abf": "stencil_kernel<ABF>", "btf": "stencil_kernel<JBF>"}[filt],
+            "kernel": {"bf": "stencil_kernel<BF>", "abf": "stencil_kernel<ABF>", "btf": "stencil_kernel<JBF>", "all": "stencil_kernel<JBF>"}[filt],
             "note": "the bilateral stencils are instruction-issue bound (see 'issue'); HBM traffic is 6-9 B/pixel"}
     if kernel_ms:
         roof["achieved"] = alg_bytes / (kernel_ms * 1e-3) / 1e9
@@ -383,7 +402,7 @@ def main():
                    "l2": f"rotating over {n_pool} distinct resident frames ({2 * n_pool * w * (s1 - s0) * 3 >> 20} MiB in+out > 126 MiB L2)",
                    "e2e": "pinned host buffers, upload + filter + download per step, two frames in flight on two streams"},
         "e2e": {"value": e2e_value, "unit": "Mpixel/s", "h2d_bytes_per_step": w * (s1 - s0) * 3 * world,
-                "d2h_bytes_per_step": w * out_rows * 3 * world, "steps": e2e_steps},
+                "d2h_bytes_per_step": w * out_rows * 3 * world * n_out, "steps": e2e_steps},
         "gpu_launches": int(launches), "kernels_per_step": kernels_per_step,
         "roofline": roof, "issue": issue, "cpu_baseline": cpu, "clocks": clocks,
     }
