@@ -51,15 +51,14 @@ struct Elem<kJBF> {
     using type = uint2;  // x = guide pixel, y = src pixel
 };
 
-// Packed fp32x2 (sm_100 FFMA2): {s0,s1} and {s2,sk} accumulate with one instruction each; sk = fma(1, w, sk) is the
-// same rounding as sk + w.  The multiplier w is a scalar operand broadcast to both halves (FFMA2 Rd, Ra.F32x2, Rb.F32, Rd).
-// Measured on B200 (tools/kbench.py): a packed instruction occupies the dispatch port like two scalar ones, so it buys
-// registers-file traffic and code size, not issue cycles: +3 % for BF/JBF.  ABF packs across two adjacent OUTPUTS
-// instead (see Acc<kABF>): +4 % (4K r=7: 0.867 -> 0.833 ms).
-template <int MODE>
-struct UseFma2 {
-    static constexpr bool value = MODE != kABF;
-};
+// Packed fp32x2 (sm_100 FFMA2 / FADD2).  {s0,s1} of one output accumulate {f0,f1} * w with the weight as the broadcast
+// scalar operand (FFMA2 Rd, Ra.F32x2, Rb.F32, Rd); s2 and sk are paired over two adjacent OUTPUTS instead:
+// {s2_i, s2_i+1} += {w_i, w_i+1} * f2 (f2 broadcast) and {sk_i, sk_i+1} += {w_i, w_i+1} (fma(w, 1, sk) rounds like
+// sk + w; ptxas emits FADD2).  The FMUL results land in an aligned register pair, so no packing MOVs are needed (the
+// first version paired {s2, sk} with the multiplicand {f2, 1.0f} and spent ~1 MOV per tap building that pair).
+// Measured on B200 (tools/kbench.py): a packed instruction occupies the dispatch port like two scalar ones, so packing
+// pays through the instructions it removes: BF 8K r=15 7.39 -> 7.00 ms, JBF 17x17 0.596 -> 0.565 ms.  ABF packs
+// everything across two adjacent outputs (see Acc<kABF>): 4K r=7 0.867 -> 0.833 ms.
 __device__ __forceinline__ unsigned long long pack2(const float lo, const float hi) {
     unsigned long long r;
     asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
@@ -80,10 +79,10 @@ __device__ __forceinline__ unsigned long long add2(const unsigned long long a, c
 
 template <int MODE, int P>
 struct Acc {
-    float s0[UseFma2<MODE>::value ? 1 : P], s1[UseFma2<MODE>::value ? 1 : P], s2[UseFma2<MODE>::value ? 1 : P],
-        sk[UseFma2<MODE>::value ? 1 : P];
-    unsigned long long s01[UseFma2<MODE>::value ? P : 1], s2k[UseFma2<MODE>::value ? P : 1];
-    std::uint32_t c[P];             // BF/JBF: packed centre (range source)
+    unsigned long long s01[P];      // {s0, s1} of output i: multiplicand {f0, f1}, weight as the broadcast scalar
+    unsigned long long s2[P / 2];   // {s2 of output 2p, s2 of output 2p+1}: multiplicand {w_2p, w_2p+1}, f2 broadcast
+    unsigned long long sk[P / 2];   // {sk of output 2p, sk of output 2p+1}: + {w_2p, w_2p+1}
+    std::uint32_t c[P];             // packed centre (range source)
 };
 
 // ABF: every quantity is a pair over two horizontally adjacent outputs (2p, 2p+1), so that one packed fp32x2
@@ -132,6 +131,12 @@ __device__ __forceinline__ void run_taps(const typename Elem<MODE>::type* __rest
         w[4 * j + 2] = v.z;
         w[4 * j + 3] = v.w;
     }
+    const unsigned long long one2 = pack2(1.f, 1.f);
+    auto weight = [&](const std::uint32_t q, const std::uint32_t c, const float ks) {
+        std::uint32_t sad = __vsadu4(q, c);
+        if constexpr (CLAMP) sad = min(sad, clamp_i);
+        return __fmul_rn(ks, lds_f32(lut_addr + (sad << 7)));
+    };
 #pragma unroll
     for (int n = 0; n < P + L - 1; ++n) {
         std::uint32_t q, v;
@@ -146,32 +151,37 @@ __device__ __forceinline__ void run_taps(const typename Elem<MODE>::type* __rest
         const float f0 = byte_to_float<0>(v);
         const float f1 = byte_to_float<1>(v);
         const float f2 = byte_to_float<2>(v);
-        unsigned long long f01 = 0, f21 = 0;
-        if constexpr (UseFma2<MODE>::value) {
-            f01 = pack2(f0, f1);
-            f21 = pack2(f2, 1.f);
-        }
+        const unsigned long long f01 = pack2(f0, f1);
 #pragma unroll
-        for (int i = 0; i < P; ++i) {
-            const int j = n - i;
-            if (j >= 0 && j < L) {
-                std::uint32_t addr;
-                {
-                    std::uint32_t sad = __vsadu4(q, A.c[i]);
-                    if constexpr (CLAMP) sad = min(sad, clamp_i);
-                    addr = lut_addr + (sad << 7);
-                }
-                const float wt = __fmul_rn(w[j], lds_f32(addr));
-                if constexpr (UseFma2<MODE>::value) {
-                    const unsigned long long ww = pack2(wt, wt);
-                    fma2(A.s01[i], f01, ww);
-                    fma2(A.s2k[i], f21, ww);
+        for (int p = 0; p < P / 2; ++p) {
+            const int j = n - 2 * p;  // tap of output 2p; output 2p+1 sees tap j-1
+            const bool lo = j >= 0 && j < L, hi = j - 1 >= 0 && j - 1 < L;
+            float wl = 0.f, wh = 0.f;
+            if (lo) {
+                wl = weight(q, A.c[2 * p], w[j]);
+                fma2(A.s01[2 * p], f01, pack2(wl, wl));
+            }
+            if (hi) {
+                wh = weight(q, A.c[2 * p + 1], w[j - 1]);
+                fma2(A.s01[2 * p + 1], f01, pack2(wh, wh));
+            }
+            if (lo && hi) {
+                const unsigned long long ww = pack2(wl, wh);
+                fma2(A.s2[p], ww, pack2(f2, f2));
+                fma2(A.sk[p], ww, one2);
+            } else if (lo || hi) {
+                float x2, y2, xk, yk;
+                unpack2(A.s2[p], x2, y2);
+                unpack2(A.sk[p], xk, yk);
+                if (lo) {
+                    x2 = __fmaf_rn(f2, wl, x2);
+                    xk = __fadd_rn(xk, wl);
                 } else {
-                    A.s0[i] = __fmaf_rn(f0, wt, A.s0[i]);
-                    A.s1[i] = __fmaf_rn(f1, wt, A.s1[i]);
-                    A.s2[i] = __fmaf_rn(f2, wt, A.s2[i]);
-                    A.sk[i] = __fadd_rn(A.sk[i], wt);
+                    y2 = __fmaf_rn(f2, wh, y2);
+                    yk = __fadd_rn(yk, wh);
                 }
+                A.s2[p] = pack2(x2, y2);
+                A.sk[p] = pack2(xk, yk);
             }
         }
     }
@@ -461,20 +471,17 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
         } else {
 #pragma unroll
             for (int i = 0; i < P; ++i) {
-                if constexpr (UseFma2<MODE>::value) {
-                    A.s01[i] = 0ull;
-                    A.s2k[i] = 0ull;
-                } else {
-                    A.s0[i] = 0.f;
-                    A.s1[i] = 0.f;
-                    A.s2[i] = 0.f;
-                    A.sk[i] = 0.f;
-                }
+                A.s01[i] = 0ull;
                 if constexpr (MODE == kJBF) {
                     A.c[i] = tcentre[i].x;
                 } else {
                     A.c[i] = tcentre[i];
                 }
+            }
+#pragma unroll
+            for (int p2 = 0; p2 < P / 2; ++p2) {
+                A.s2[p2] = 0ull;
+                A.sk[p2] = 0ull;
             }
         }
 
@@ -499,11 +506,13 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
                     for (int c = 0; c < 4; ++c) unpack2(A.s[c][i / 2], x[c], y[c]);
                     s0 = (i & 1) ? y[0] : x[0], s1 = (i & 1) ? y[1] : x[1], s2 = (i & 1) ? y[2] : x[2],
                     sk = (i & 1) ? y[3] : x[3];
-                } else if constexpr (UseFma2<MODE>::value) {
-                    unpack2(A.s01[i], s0, s1);
-                    unpack2(A.s2k[i], s2, sk);
                 } else {
-                    s0 = A.s0[i], s1 = A.s1[i], s2 = A.s2[i], sk = A.sk[i];
+                    float x2, y2, xk, yk;
+                    unpack2(A.s01[i], s0, s1);
+                    unpack2(A.s2[i / 2], x2, y2);
+                    unpack2(A.sk[i / 2], xk, yk);
+                    s2 = (i & 1) ? y2 : x2;
+                    sk = (i & 1) ? yk : xk;
                 }
                 o[3 * i + 0] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(s0, sk), 0.5f));
                 o[3 * i + 1] = static_cast<std::uint8_t>(__fadd_rn(__fdiv_rn(s1, sk), 0.5f));
