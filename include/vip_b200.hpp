@@ -147,6 +147,43 @@ private:
     vip_image* table_;
 };
 
+// BorderReplicatedIntegralImage<SrcType, Channels> on the GPU for every instantiation the reference tests
+// (test/border_replicated_integral_image.cpp:63-95): uint8_t / uint16_t sources -> uint32 table (modulo 2^32),
+// float -> float table.  Header-only on top of vip_integral_build / vip_integral_get.
+template <typename SrcType, int Channels>
+class CudaBorderReplicatedIntegralImage {
+    static_assert(std::is_same<SrcType, std::uint8_t>::value || std::is_same<SrcType, std::uint16_t>::value ||
+                      std::is_same<SrcType, float>::value, "uint8_t, uint16_t or float");
+    static_assert(Channels >= 1 && Channels <= 4, "1..4 channels");
+
+public:
+    using AccType = typename std::conditional<std::is_same<SrcType, float>::value, float, std::uint32_t>::type;
+    static constexpr int kSrcType = std::is_same<SrcType, float>::value ? VIP_SRC_F32
+                                    : (std::is_same<SrcType, std::uint16_t>::value ? VIP_SRC_U16 : VIP_SRC_U8);
+
+    CudaBorderReplicatedIntegralImage(const int width, const int height, const int radius)
+        : width_(width), height_(height), radius_(radius), table_(nullptr) {
+        vip_image_create(&table_, width + 2 * radius + 1, height + 2 * radius + 1, Channels, 4);
+    }
+    ~CudaBorderReplicatedIntegralImage() { vip_image_destroy(table_); }
+    CudaBorderReplicatedIntegralImage(const CudaBorderReplicatedIntegralImage&) = delete;
+    CudaBorderReplicatedIntegralImage& operator=(const CudaBorderReplicatedIntegralImage&) = delete;
+
+    int build(const SrcType* d_src, void* stream = nullptr) {
+        return vip_integral_build(d_src, vip_image_data(table_), width_, height_, Channels, radius_, kSrcType, stream);
+    }
+    // n rectangles (x0, y0, x1, y1) on the device -> n x Channels inclusive box sums (get(), :34-47)
+    int get(const std::int32_t* d_rects, int n, AccType* d_out, void* stream = nullptr) const {
+        return vip_integral_get(vip_image_data(table_), width_, height_, Channels, radius_, kSrcType, d_rects, n, d_out,
+                                stream);
+    }
+    const AccType* table() const { return static_cast<const AccType*>(vip_image_data(table_)); }
+
+private:
+    int width_, height_, radius_;
+    vip_image* table_;
+};
+
 // Row strips with halo exchange / frame batches over the GPUs of one box (vip_mg_* in vip_c_api.h).
 class VIP_API MultiGpuFilter {
 public:

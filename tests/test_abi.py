@@ -92,6 +92,8 @@ def test_cpp_dropin_headers_compile_without_cuda(tmp_path):
                    "  CudaAdaptiveBilateralFilter g(w, h); g.execute(a.get(), b.get());\n"
                    "  CudaBilateralTextureFilter t(w, h, 9, 3); t.execute(a.get(), b.get());\n"
                    "  DeviceImage<float> m(w, h); cuda_gradient(a.get(), m.get(), w, h, 3);\n"
+                   "  CudaBorderReplicatedIntegralImage<std::uint8_t, 3> ii(w, h, 7); ii.build(a.get());\n"
+                   "  CudaBorderReplicatedIntegralImage<float, 1> fi(w, h, 2); fi.build(m.get());\n"
                    "  b.download(out); return 0; }\n")
     so = tmp_path / "libuser.so"
     subprocess.check_call(["g++", "-std=c++17", "-shared", "-fPIC", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(so),
