@@ -11,7 +11,7 @@ strips with radius-deep halos, strong scaling), btf_4k (configs[2]), bf_lenna (c
 abf_1080p / btf_1080p (configs[4] frames).
 
 One JSON line on stdout.  `value` = whole-job Mpixel/s with inputs resident in HBM; `e2e` = the same through the
-public API with pinned HOST buffers, H2D + kernel + D2H inside the timed region, two frames in flight; `roofline` =
+public API with pinned HOST buffers, H2D + kernel + D2H inside the timed region, four frames in flight; `roofline` =
 the dominant kernel against the measured HBM peak (MEASURED_PEAKS.json) -- the stencil kernels are issue-bound, not
 HBM-bound, so `issue` gives the achieved taps/s and the estimated issue-slot utilisation next to it; `cpu_baseline`
 = the reference's own C++ CPU path (oracle/_ref/libvip_ref_cpu.so, compiled unmodified from the reference) on a
@@ -288,22 +288,23 @@ def main():
     value = pixels_step / (ms_step * 1e-3) / 1e6
 
     # ---- end to end through the public API with pinned host buffers, two frames in flight
-    e2e_steps = max(4, min(args.steps, 20))
+    e2e_steps = max(8, min(args.steps, 40))
     slots = []
-    for s in range(2):
+    NS = 4   # frames in flight: upload, filter and download of different frames overlap on NS streams
+    for s in range(NS):
         src_img, dst_img = vip.DeviceImage(w, s1 - s0, 3), vip.DeviceImage(w, out_rows, 3)
         hin, hout = vip.PinnedBuffer(w * (s1 - s0) * 3), vip.PinnedBuffer(w * out_rows * 3)
         hin.array[:] = frames[s % n_pool][s0:s1].reshape(-1)
         slots.append((src_img, dst_img, hin, hout, torch.cuda.Stream()))
     if filt == "btf":
-        F2 = [F, vip.CudaBilateralTextureFilter(w, h, ksize, nitr)]   # scratch is per object
+        F2 = [F] + [vip.CudaBilateralTextureFilter(w, h, ksize, nitr) for _ in range(NS - 1)]   # scratch is per object
     n_out = 3 if filt == "all" else 1                                 # result images downloaded per step
     if filt == "all":
-        F2 = [F[2], vip.CudaBilateralTextureFilter(w, h, ksize, nitr)]
-        extra = [[(vip.DeviceImage(w, out_rows, 3), vip.PinnedBuffer(w * out_rows * 3)) for _ in range(2)] for _ in range(2)]
+        F2 = [F[2]] + [vip.CudaBilateralTextureFilter(w, h, ksize, nitr) for _ in range(NS - 1)]
+        extra = [[(vip.DeviceImage(w, out_rows, 3), vip.PinnedBuffer(w * out_rows * 3)) for _ in range(2)] for _ in range(NS)]
 
     def e2e_step(i):
-        src_img, dst_img, hin, hout, st = slots[i & 1]
+        src_img, dst_img, hin, hout, st = slots[i % NS]
         src_img.upload(hin.array, stream=st)
         if filt == "bf":
             if strong:
@@ -313,17 +314,17 @@ def main():
         elif filt == "abf":
             F.execute_async(src_img, dst_img, stream=st)
         elif filt == "btf":
-            F2[i & 1].execute_async(src_img, dst_img, stream=st)
+            F2[i % NS].execute_async(src_img, dst_img, stream=st)
         else:
-            (d2, h2), (d3, h3) = extra[i & 1]
+            (d2, h2), (d3, h3) = extra[i % NS]
             F[0].bilateral_filter_async(src_img, dst_img, stream=st)
             F[1].execute_async(src_img, d2, stream=st)
-            F2[i & 1].execute_async(src_img, d3, stream=st)
+            F2[i % NS].execute_async(src_img, d3, stream=st)
             d2.download(h2.array, stream=st)
             d3.download(h3.array, stream=st)
         dst_img.download(hout.array, stream=st)
 
-    for i in range(2):
+    for i in range(NS):
         e2e_step(i)
     barrier()
     t0 = time.perf_counter()
@@ -400,7 +401,7 @@ def main():
         "config": {"workload": args.workload, "description": desc, "width": w, "height": h, "ksize": ksize, "nitr": nitr,
                    "content": args.content, "parallelism": ("row strips + halos" if strong else f"{world} independent frame stream(s)"),
                    "l2": f"rotating over {n_pool} distinct resident frames ({2 * n_pool * w * (s1 - s0) * 3 >> 20} MiB in+out > 126 MiB L2)",
-                   "e2e": "pinned host buffers, upload + filter + download per step, two frames in flight on two streams"},
+                   "e2e": "pinned host buffers, upload + filter + download per step, four frames in flight on four streams"},
         "e2e": {"value": e2e_value, "unit": "Mpixel/s", "h2d_bytes_per_step": w * (s1 - s0) * 3 * world,
                 "d2h_bytes_per_step": w * out_rows * 3 * world * n_out, "steps": e2e_steps},
         "gpu_launches": int(launches), "kernels_per_step": kernels_per_step,

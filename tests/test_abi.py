@@ -99,3 +99,11 @@ def test_cpp_dropin_headers_compile_without_cuda(tmp_path):
     subprocess.check_call(["g++", "-std=c++17", "-shared", "-fPIC", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(so),
                            "-L", os.path.dirname(capi.LIB_PATH), "-lvip_b200"])
     assert so.exists()
+
+
+def test_division_by_constant_shortcut_is_exact(tmp_path):
+    """csrc/btf.cu replaces __fdiv_rn(x, K*K) and __fdiv_rn(x, 3.f) by a 3-instruction sequence; exhaustive proof."""
+    exe = tmp_path / "div_const_check"
+    subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", os.path.join(ROOT, "tests", "div_const_check.c"), "-o", str(exe), "-lm"])
+    out = subprocess.check_output([str(exe)], text=True)
+    assert "mismatches 0" in out

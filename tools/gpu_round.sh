@@ -20,4 +20,9 @@ for wl in abf_4k_r7 btf_4k bf_8k_r15; do
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:'stencil_kernel|blur_rtv|guide_kernel' -s 6 -c 3 -f -o $O/full_$wl \
     python bench.py --workload $wl --steps 4 --warmup 3 --no-cpu-baseline > $O/ncu_full_$wl.log 2>&1
 done
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:'gradient|integral' -s 8 -c 4 -f -o $O/full_streaming \
+  python tools/kbench.py grad:3840x2160:3 integral:3840x2160:7 > $O/ncu_full_streaming.log 2>&1
+timeout 300 python bench.py --workload stream_1080p --steps 128 > $O/bench_stream_1080p.json 2> $O/bench_stream_1080p.err
+timeout 300 python bench.py --workload bf_lenna --steps 200 > $O/bench_bf_lenna.json 2> $O/bench_bf_lenna.err
+timeout 300 python bench.py --impl reference --workload bf_lenna --steps 3 --warmup 1 > $O/bench_reference_lenna.json 2> $O/bench_reference_lenna.err
 echo done > $O/round_done.txt
