@@ -291,6 +291,29 @@ def test_btf_end_to_end(vip, w, h, k, nitr):
         assert (d > 1).mean() < 0.02, f"{(d > 1).mean():.4f} of samples differ by more than 1 LSB from the CPU reference"
 
 
+@pytest.mark.parametrize("off", [1, 2, 3])
+@pytest.mark.parametrize("w,h", [(203, 77), (256, 64)])
+def test_unaligned_buffers(vip, off, w, h):
+    """The reference promises no alignment: source / guide / destination at odd byte offsets, every row
+    alignment (w*3 mod 4) -- exercises all four cases of the vectorised tile staging."""
+    img, guide = O.rand_image(w, h, seed=off), O.rand_image(w, h, seed=off + 10)
+    n = w * h * 3
+    bs = torch.zeros(n + 8, dtype=torch.uint8, device="cuda")
+    bg = torch.zeros(n + 8, dtype=torch.uint8, device="cuda")
+    bd = torch.zeros(n + 8, dtype=torch.uint8, device="cuda")
+    bs[off:off + n] = dev(img).reshape(-1)
+    bg[off + 1:off + 1 + n] = dev(guide).reshape(-1)
+    src, gd, dst = bs[off:off + n], bg[off + 1:off + 1 + n], bd[(off + 2) % 4:(off + 2) % 4 + n]
+    f = vip.CudaBilateralFilter(w, h, 11)
+    f.bilateral_filter(src, dst)
+    assert np.array_equal(dst.cpu().numpy().reshape(h, w, 3), O.o_bf(img, 11))
+    f.joint_bilateral_filter(src, gd, dst)
+    assert np.array_equal(dst.cpu().numpy().reshape(h, w, 3), O.o_jbf(img, guide, 11))
+    vip.CudaAdaptiveBilateralFilter(w, h, 9).execute(src, dst)
+    assert np.array_equal(dst.cpu().numpy().reshape(h, w, 3), O.o_abf(img, 9))
+    assert int(bd[(off + 2) % 4 + n:].max()) == 0 and int(bd[:(off + 2) % 4].sum()) == 0     # nothing written outside
+
+
 # ------------------------------------------------------------------ host-I/O edge (sample/benchmark/main.cpp:91-103)
 @pytest.mark.parametrize("w,h", [(1, 1), (7, 3), (64, 64), (1921, 1079)])
 @pytest.mark.parametrize("ch,swap", [(1, False), (3, False), (3, True), (4, False), (4, True)])

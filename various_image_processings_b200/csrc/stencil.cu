@@ -102,6 +102,22 @@ __device__ __forceinline__ std::uint32_t load_packed(const std::uint8_t* __restr
            (static_cast<std::uint32_t>(__ldg(p + 2)) << 16);
 }
 
+// Four consecutive packed BGR pixels (12 bytes at ANY byte alignment) -> four 32-bit B|G<<8|R<<16 words, from aligned
+// 32-bit loads: the 16-byte window that contains them is read as 3 (aligned case) or 4 words, realigned with three
+// funnel shifts and cut with four more.  The 4th word is only touched when the data straddle it.
+__device__ __forceinline__ void load_packed4(const std::uint8_t* __restrict__ p, std::uint32_t out[4]) {
+    const unsigned m = static_cast<unsigned>(reinterpret_cast<std::uintptr_t>(p) & 3u);
+    const std::uint32_t* w = reinterpret_cast<const std::uint32_t*>(p - m);
+    const std::uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+    const std::uint32_t w3 = m ? __ldg(w + 3) : 0u;
+    const unsigned sh = 8u * m;
+    const std::uint32_t v0 = __funnelshift_r(w0, w1, sh), v1 = __funnelshift_r(w1, w2, sh), v2 = __funnelshift_r(w2, w3, sh);
+    out[0] = v0 & 0x00ffffffu;
+    out[1] = __funnelshift_r(v0, v1, 24) & 0x00ffffffu;
+    out[2] = __funnelshift_r(v1, v2, 16) & 0x00ffffffu;
+    out[3] = v2 >> 8;
+}
+
 __device__ __forceinline__ float lds_f32(const std::uint32_t addr) {
     float v;
     asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
@@ -371,7 +387,6 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
     const float clamp_f = static_cast<float>(a.lut_n - 1);
     const int W = a.width, H = a.height;
     const int tw = L.tile_w, th = L.tile_h, tp = L.tile_pitch;
-    const int step_x = kThreads % tw, step_y = kThreads / tw;
 
     // Tiles blockIdx.x, blockIdx.x + gridDim.x, ... belong to this CTA (every SM gets the same number +-1); its warp
     // groups take them in order from a shared-memory counter, so a group that finishes early picks up the next tile.
@@ -385,23 +400,44 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
         const int X0 = tile_x * (kWarps * P);
         const int Y0 = a.out_y0 + tile_y * kTileRows;
 
+        // clamp to the image, then (rows no valid output depends on) to the rows the buffers hold
+        auto buffer_row = [&](const int ey) {
+            return clampi(clampi(Y0 - radius + ey, 0, H - 1), a.src_y0, a.src_y0 + a.src_rows - 1) - a.src_y0;
+        };
+        // Tiles whose columns (plus one spare pixel to the right, which the 4th word of load_packed4 may touch) lie
+        // inside the image are staged 4 pixels at a time from aligned 32-bit loads; border tiles and the tw % 4
+        // leftover columns go pixel by pixel with clamped coordinates.
+        const bool interior = X0 - radius >= 0 && X0 - radius + tw < W;
+        const int vec_cols = interior ? (tw & ~3) : 0;
+        if (interior) {
+            const int gpr = tw >> 2;
+            for (int item = tid; item < th * gpr; item += kThreads) {
+                const int ey = item / gpr, g = item - ey * gpr;
+                const size_t o = (static_cast<size_t>(buffer_row(ey)) * W + (X0 - radius + 4 * g)) * 3;
+                std::uint32_t v[4];
+                load_packed4(a.src + o, v);
+                E* const trow = tile + ey * tp + 4 * g;
+                if constexpr (MODE == kJBF) {
+                    std::uint32_t q[4];
+                    load_packed4(a.guide + o, q);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) trow[j] = make_uint2(q[j], v[j]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) trow[j] = v[j];
+                }
+            }
+        }
         {
-            int ex = tid % tw, ey = tid / tw;
-            while (ey < th) {
+            const int rem = tw - vec_cols;  // columns [vec_cols, tw) of every row
+            for (int item = tid; item < th * rem; item += kThreads) {
+                const int ey = item / rem, ex = vec_cols + (item - ey * rem);
                 const int gx = clampi(X0 - radius + ex, 0, W - 1);
-                // clamp to the image, then (rows no valid output depends on) to the rows the buffers hold
-                const int gy = clampi(clampi(Y0 - radius + ey, 0, H - 1), a.src_y0, a.src_y0 + a.src_rows - 1) - a.src_y0;
-                const size_t o = (static_cast<size_t>(gy) * W + gx) * 3;
+                const size_t o = (static_cast<size_t>(buffer_row(ey)) * W + gx) * 3;
                 if constexpr (MODE == kJBF) {
                     tile[ey * tp + ex] = make_uint2(load_packed(a.guide + o), load_packed(a.src + o));
                 } else {
                     tile[ey * tp + ex] = load_packed(a.src + o);
-                }
-                ex += step_x;
-                ey += step_y;
-                if (ex >= tw) {
-                    ex -= tw;
-                    ey += 1;
                 }
             }
         }
