@@ -35,7 +35,7 @@ namespace vip {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kTW = 64;    // tile columns: 2 warps side by side
+constexpr int kTW = 64;    // tile columns: 2 warps side by side (the blur/mRTV horizontal pass assumes 8 groups of 8)
 constexpr int kTH = 32;    // tile rows:    4 warp rows x 8 rows per thread
 constexpr int kRows = 8;   // consecutive output rows per thread
 
@@ -44,6 +44,20 @@ __device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? l
 __device__ __forceinline__ std::uint32_t load_packed(const std::uint8_t* __restrict__ p) {
     return static_cast<std::uint32_t>(__ldg(p)) | (static_cast<std::uint32_t>(__ldg(p + 1)) << 8) |
            (static_cast<std::uint32_t>(__ldg(p + 2)) << 16);
+}
+
+// Four consecutive packed BGR pixels (12 bytes at any byte alignment) from aligned 32-bit loads (see stencil.cu)
+__device__ __forceinline__ void load_packed4(const std::uint8_t* __restrict__ p, std::uint32_t out[4]) {
+    const unsigned m = static_cast<unsigned>(reinterpret_cast<std::uintptr_t>(p) & 3u);
+    const std::uint32_t* w = reinterpret_cast<const std::uint32_t*>(p - m);
+    const std::uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+    const std::uint32_t w3 = m ? __ldg(w + 3) : 0u;
+    const unsigned sh = 8u * m;
+    const std::uint32_t v0 = __funnelshift_r(w0, w1, sh), v1 = __funnelshift_r(w1, w2, sh), v2 = __funnelshift_r(w2, w3, sh);
+    out[0] = v0 & 0x00ffffffu;
+    out[1] = __funnelshift_r(v0, v1, 24) & 0x00ffffffu;
+    out[2] = __funnelshift_r(v1, v2, 16) & 0x00ffffffu;
+    out[3] = v2 >> 8;
 }
 
 // sum over the three colour bytes of (a_c - b_c)^2, exact
@@ -69,7 +83,8 @@ struct BlurLayout {
     static constexpr int MW = kTW + 2 * r, MH = kTH + 2 * r;          // magnitudes / records, radius halo
     static constexpr int pix_off = 0;
     static constexpr int mag_off = (PW * PH * 4 + 15) & ~15;
-    static constexpr int hs_off = (mag_off + MW * MH * 4 + 15) & ~15;
+    static constexpr int MP = MW + 2;   // magnitude row pitch: rows 10 banks apart (as the pixels), not 8
+    static constexpr int hs_off = (mag_off + MP * MH * 4 + 15) & ~15;
     static constexpr int total = hs_off + MH * kTW * 16;
 };
 
@@ -102,18 +117,35 @@ __global__ void __launch_bounds__(kThreads, 3) blur_rtv_kernel(const std::uint8_
     const RowMap rowmap{H, src_y0, src_rows};
 
     // A. packed pixels of [X0-r-1, X0+kTW+r+1) x [Y0-r-1, Y0+kTH+r+1), coordinates clamped to the image
-    for (int e = tid; e < L::PW * L::PH; e += kThreads) {
-        const int ey = e / L::PW, ex = e - ey * L::PW;
-        const int gx = clampi(X0 - r - 1 + ex, 0, W - 1);
-        const int gy = rowmap(Y0 - r - 1 + ey);
-        pix[e] = load_packed(image + (static_cast<size_t>(gy) * W + gx) * 3);
+    //    interior tiles: 4 pixels per thread from aligned 32-bit loads; border tiles / leftover columns pixel by pixel
+    const bool interior = X0 - r - 1 >= 0 && X0 - r - 1 + L::PW < W;
+    constexpr int kGroups = L::PW / 4;
+    const int vec_cols = interior ? kGroups * 4 : 0;
+    if (interior) {
+        for (int item = tid; item < L::PH * kGroups; item += kThreads) {
+            const int ey = item / kGroups, g = item - ey * kGroups;
+            const int gy = rowmap(Y0 - r - 1 + ey);
+            std::uint32_t v[4];
+            load_packed4(image + (static_cast<size_t>(gy) * W + (X0 - r - 1 + 4 * g)) * 3, v);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) pix[ey * L::PW + 4 * g + j] = v[j];
+        }
+    }
+    {
+        const int rem = L::PW - vec_cols;
+        for (int item = tid; item < L::PH * rem; item += kThreads) {
+            const int ey = item / rem, ex = vec_cols + (item - ey * rem);
+            const int gx = clampi(X0 - r - 1 + ex, 0, W - 1);
+            const int gy = rowmap(Y0 - r - 1 + ey);
+            pix[ey * L::PW + ex] = load_packed(image + (static_cast<size_t>(gy) * W + gx) * 3);
+        }
     }
     if constexpr (!FUSED) {
         for (int e = tid; e < L::MW * L::MH; e += kThreads) {
             const int my = e / L::MW, mx = e - my * L::MW;
             const int gx = clampi(X0 - r + mx, 0, W - 1);
             const int gy = rowmap(Y0 - r + my);
-            mag[e] = __ldg(magnitude + static_cast<size_t>(gy) * W + gx);
+            mag[my * L::MP + mx] = __ldg(magnitude + static_cast<size_t>(gy) * W + gx);
         }
     }
     __syncthreads();
@@ -129,29 +161,85 @@ __global__ void __launch_bounds__(kThreads, 3) blur_rtv_kernel(const std::uint8_
             const int xm = cx > 0 ? -1 : 0, xp = cx < W - 1 ? 1 : 0;
             const int ym = cy > 0 ? -L::PW : 0, yp = cy < H - 1 ? L::PW : 0;
             const int acc = sq_diff(c[xp], c[xm]) + sq_diff(c[yp], c[ym]);
-            mag[e] = sqrtf(static_cast<float>(acc));
+            mag[my * L::MP + mx] = sqrtf(static_cast<float>(acc));
         }
         __syncthreads();
     }
 
-    // C. horizontal pass: record = {B | R<<16, G, min(b+g+r) | max(b+g+r)<<16, max magnitude} over K columns
-    for (int e = tid; e < L::MH * kTW; e += kThreads) {
-        const int row = e / kTW, col = e - row * kTW;
-        const std::uint32_t* pr = pix + (row + 1) * L::PW + col + 1;
-        const float* mr = mag + row * L::MW + col;
-        std::uint32_t br = 0, g = 0, mn = 0xffffu, mx = 0;
-        float mm = 0.f;
+    // C. horizontal pass: record = {B | R<<16, G, min(b+g+r) | max(b+g+r)<<16, max magnitude} over K columns.
+    //    A thread produces the records of 8 adjacent columns of one row from K+7 pixels / magnitudes held in
+    //    registers: the two sums slide (add the entering, subtract the leaving pixel), min / max / fmax of a K-window
+    //    are two overlapping power-of-two windows built by doubling (all exact, order-independent operations).
+    {
+        constexpr int N = K + 7;                       // inputs of 8 outputs
+        constexpr int Q = K >= 8 ? 8 : (K >= 4 ? 4 : (K >= 2 ? 2 : 1));   // largest power of two <= K
+        for (int item = tid; item < L::MH * (kTW / 8); item += kThreads) {
+            const int cg = item & 7, row = item >> 3, col0 = cg * 8;   // kTW / 8 == 8 column groups
+            const std::uint32_t* pr = pix + (row + 1) * L::PW + col0 + 1;
+            const float* mr = mag + row * L::MP + col0;
+            std::uint32_t br[8], g[8], lh[8];
+            float fm[8];
+            {
+                std::uint32_t p[N];
 #pragma unroll
-        for (int j = 0; j < K; ++j) {
-            const std::uint32_t p = pr[j];
-            const std::uint32_t s = __vsadu4(p, 0u);
-            br += __byte_perm(p, 0u, 0x4240);
-            g += __byte_perm(p, 0u, 0x4441);
-            mn = min(mn, s);
-            mx = max(mx, s);
-            mm = fmaxf(mm, mr[j]);
+                for (int j = 0; j < N; ++j) p[j] = pr[j];
+                std::uint32_t sb = 0, sg = 0;
+#pragma unroll
+                for (int j = 0; j < K; ++j) {
+                    sb += __byte_perm(p[j], 0u, 0x4240);
+                    sg += __byte_perm(p[j], 0u, 0x4441);
+                }
+                br[0] = sb;
+                g[0] = sg;
+#pragma unroll
+                for (int i = 1; i < 8; ++i) {
+                    sb += __byte_perm(p[i + K - 1], 0u, 0x4240) - __byte_perm(p[i - 1], 0u, 0x4240);
+                    sg += __byte_perm(p[i + K - 1], 0u, 0x4441) - __byte_perm(p[i - 1], 0u, 0x4441);
+                    br[i] = sb;
+                    g[i] = sg;
+                }
+                {
+                    std::uint32_t a[N];
+#pragma unroll
+                    for (int j = 0; j < N; ++j) a[j] = __vsadu4(p[j], 0u);
+#pragma unroll
+                    for (int d = 1; d < Q; d <<= 1) {
+#pragma unroll
+                        for (int j = 0; j + d < N; ++j) a[j] = min(a[j], a[j + d]);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) lh[i] = min(a[i], a[i + K - Q]);
+                }
+                {
+                    std::uint32_t c[N];
+#pragma unroll
+                    for (int j = 0; j < N; ++j) c[j] = __vsadu4(p[j], 0u);
+#pragma unroll
+                    for (int d = 1; d < Q; d <<= 1) {
+#pragma unroll
+                        for (int j = 0; j + d < N; ++j) c[j] = max(c[j], c[j + d]);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) lh[i] |= max(c[i], c[i + K - Q]) << 16;
+                }
+            }
+            {
+                float f[N];
+#pragma unroll
+                for (int j = 0; j < N; ++j) f[j] = mr[j];
+#pragma unroll
+                for (int d = 1; d < Q; d <<= 1) {
+#pragma unroll
+                    for (int j = 0; j + d < N; ++j) f[j] = fmaxf(f[j], f[j + d]);
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) fm[i] = fmaxf(fmaxf(f[i], f[i + K - Q]), 0.f);   // the reference's max starts at 0
+            }
+            uint4* hrow = hs + row * kTW + col0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i)   // rotated inside the group of 8: the 8 lanes of a quarter warp hit 8 different 16-byte slots
+                hrow[(i + cg) & 7] = make_uint4(br[i], g[i], lh[i], __float_as_uint(fm[i]));
         }
-        hs[e] = make_uint4(br, g, mn | (mx << 16), __float_as_uint(mm));
     }
     __syncthreads();
 
@@ -170,10 +258,10 @@ __global__ void __launch_bounds__(kThreads, 3) blur_rtv_kernel(const std::uint8_
     }
 #pragma unroll
     for (int R = 0; R < K + kRows - 1; ++R) {
-        const uint4 h = hs[(r0 + R) * kTW + col];
+        const uint4 h = hs[(r0 + R) * kTW + (col & ~7) + ((col + (col >> 3)) & 7)];
         float v[K];
 #pragma unroll
-        for (int j = 0; j < K; ++j) v[j] = mag[(r0 + R) * L::MW + col + j];
+        for (int j = 0; j < K; ++j) v[j] = mag[(r0 + R) * L::MP + col + j];
 #pragma unroll
         for (int i = 0; i < kRows; ++i) {
             if (R - i >= 0 && R - i < K) {
