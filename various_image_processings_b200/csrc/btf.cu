@@ -351,31 +351,41 @@ __global__ void blur_rtv_generic_kernel(const std::uint8_t* __restrict__ image, 
     rtv[o] = static_cast<float>(static_cast<double>(num) / (static_cast<double>(msum) + 1e-9));
 }
 
+// 4-byte asynchronous global -> shared copy (LDGSTS): no register staging, any number in flight
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(static_cast<std::uint32_t>(__cvta_generic_to_shared(smem_dst))),
+                 "l"(gmem_src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
 template <int K>
 struct GuideLayout {
     static constexpr int r = K / 2;
     static constexpr int MW = kTW + 2 * r, MH = kTH + 2 * r;
     static constexpr int hs_off = (MW * MH * 4 + 15) & ~15;
     static constexpr int out_off = hs_off + MH * kTW * 8;
-    static constexpr int total = out_off + kTH * kTW * 3;
+    static constexpr int bl_off = (out_off + kTH * kTW * 3 + 15) & ~15;   // blurred tile + halo: MH x MW x 3 floats
+    static constexpr int total = bl_off + MW * MH * 12;
 };
 
-// alpha and the blend of one guide pixel (:167-176); bq / bp point at the 3 blurred floats of the argmin / centre pixel
+// alpha and the blend of one guide pixel (:167-176); bq / bp are the 3 blurred floats of the argmin / centre pixel
 __device__ __forceinline__ void guide_pixel(const float rtv_p, const float rtv_min, const float sigma_alpha,
-                                            const float* __restrict__ bq, const float* __restrict__ bp,
-                                            std::uint8_t* out) {
+                                            const float bq[3], const float bp[3], std::uint8_t* out) {
     const float e = expf(__fmul_rn(sigma_alpha, __fsub_rn(rtv_p, rtv_min)));
     const float alpha = __fsub_rn(__fdiv_rn(2.f, __fadd_rn(1.f, e)), 1.f);
     const float one_m = __fsub_rn(1.f, alpha);
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-        const float t = __fadd_rn(__fmaf_rn(alpha, __ldg(bq + c), __fmul_rn(one_m, __ldg(bp + c))), 0.5f);
+        const float t = __fadd_rn(__fmaf_rn(alpha, bq[c], __fmul_rn(one_m, bp[c])), 0.5f);
         out[c] = static_cast<std::uint8_t>(clampi(__float2int_rz(t), 0, 255));
     }
 }
 
 template <int K>
-__global__ void __launch_bounds__(kThreads, 4) guide_kernel(const float* __restrict__ blurred,
+__global__ void __launch_bounds__(kThreads, 3) guide_kernel(const float* __restrict__ blurred,
                                                            const float* __restrict__ rtv, std::uint8_t* __restrict__ guide,
                                                            const int W, const int H, const int src_y0, const int src_rows,
                                                            const int dst_y0, const int out_y0, const int out_rows) {
@@ -385,16 +395,43 @@ __global__ void __launch_bounds__(kThreads, 4) guide_kernel(const float* __restr
     float* const tile = reinterpret_cast<float*>(smem);
     float2* const hs = reinterpret_cast<float2*>(smem + L::hs_off);
     std::uint8_t* const obuf = smem + L::out_off;
+    float* const bl = reinterpret_cast<float*>(smem + L::bl_off);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int X0 = blockIdx.x * kTW;
     const int Y0 = out_y0 + blockIdx.y * kTH;
     const RowMap rowmap{H, src_y0, src_rows};
 
-    for (int e = tid; e < L::MW * L::MH; e += kThreads) {
-        const int ey = e / L::MW, ex = e - ey * L::MW;
-        const int gx = clampi(X0 - r + ex, 0, W - 1);
-        tile[e] = __ldg(rtv + static_cast<size_t>(rowmap(Y0 - r + ey)) * W + gx);
+    // The rtv tile and the blurred tile (+ radius halo) go to shared memory: the argmin pixel of every output lies inside
+    // the tile, so the data-dependent gather of the reference (:168-175) becomes a shared-memory read.  Interior tiles
+    // are copied with cp.async (every copy of the tile in flight at once: the kernel waits for global memory once per
+    // tile, not once per output row as the gather version did); border tiles clamp pixel by pixel.
+    constexpr int kRowF = L::MW * 3;
+    static_assert(kRowF <= kThreads, "one thread per float of a blurred tile row");
+    const bool interior = X0 - r >= 0 && X0 - r + L::MW <= W;
+    if (interior) {
+        const int wrow = tid >> 5, lane_ = tid & 31;
+        for (int ey = wrow; ey < L::MH; ey += kThreads / 32) {       // rtv: a warp per row
+            const float* g = rtv + static_cast<size_t>(rowmap(Y0 - r + ey)) * W + (X0 - r);
+            for (int ex = lane_; ex < L::MW; ex += 32) cp_async4(tile + ey * L::MW + ex, g + ex);
+        }
+#pragma unroll 4
+        for (int ey = 0; ey < L::MH; ++ey) {                          // blurred: the CTA per row
+            const float* g = blurred + (static_cast<size_t>(rowmap(Y0 - r + ey)) * W + (X0 - r)) * 3;
+            if (tid < kRowF) cp_async4(bl + ey * kRowF + tid, g + tid);
+        }
+        cp_async_wait_all();
+    } else {
+        for (int e = tid; e < L::MW * L::MH; e += kThreads) {
+            const int ey = e / L::MW, ex = e - ey * L::MW;
+            const int gx = clampi(X0 - r + ex, 0, W - 1);
+            tile[e] = __ldg(rtv + static_cast<size_t>(rowmap(Y0 - r + ey)) * W + gx);
+        }
+        for (int e = tid; e < L::MH * kRowF; e += kThreads) {
+            const int ey = e / kRowF, t = e - ey * kRowF;
+            const int ex = t / 3, c = t - ex * 3;
+            bl[e] = __ldg(blurred + (static_cast<size_t>(rowmap(Y0 - r + ey)) * W + clampi(X0 - r + ex, 0, W - 1)) * 3 + c);
+        }
     }
     __syncthreads();
 
@@ -445,17 +482,21 @@ __global__ void __launch_bounds__(kThreads, 4) guide_kernel(const float* __restr
 #pragma unroll
     for (int i = 0; i < kRows; ++i) {
         const int y = min(Y0 + r0 + i, H - 1);
-        int mx = 0, my = 0;  // the reference's initial coordinates when nothing is below 1e10f
-        float rmin = best[i];
-        if (bj[i] >= 0) {
-            mx = clampi(x + bj[i] - r, 0, W - 1);
-            my = clampi(y + bky[i] - r, 0, H - 1);
-        } else {
-            rmin = __ldg(rtv + static_cast<size_t>(rowmap(0)) * W);
-        }
         const float rp = tile[(r0 + i + r) * L::MW + col + r];
-        const float* bq = blurred + (static_cast<size_t>(rowmap(my)) * W + mx) * 3;
-        const float* bp = blurred + (static_cast<size_t>(rowmap(y)) * W + x) * 3;
+        const float* bpp = bl + ((r0 + i + r) * L::MW + col + r) * 3;
+        const float bp[3] = {bpp[0], bpp[1], bpp[2]};
+        float rmin = best[i];
+        float bq[3];
+        if (bj[i] >= 0) {
+            // tile element (col + kx, row + ky) holds the CLAMPED pixel (:159-163), exactly what the reference gathers
+            const float* bqp = bl + ((r0 + i + bky[i]) * L::MW + col + bj[i]) * 3;
+            bq[0] = bqp[0], bq[1] = bqp[1], bq[2] = bqp[2];
+        } else {
+            // nothing below 1e10f: the reference keeps its initial coordinates (0, 0)
+            rmin = __ldg(rtv + static_cast<size_t>(rowmap(0)) * W);
+            const float* g0 = blurred + static_cast<size_t>(rowmap(0)) * W * 3;
+            bq[0] = __ldg(g0), bq[1] = __ldg(g0 + 1), bq[2] = __ldg(g0 + 2);
+        }
         guide_pixel(rp, rmin, sigma_alpha, bq, bp, obuf + ((r0 + i) * kTW + col) * 3);
     }
     __syncthreads();
@@ -504,9 +545,11 @@ __global__ void guide_generic_kernel(const float* __restrict__ blurred, const fl
     const float rq = __ldg(rtv + static_cast<size_t>(rowmap(my)) * W + mx);
     const float rp = __ldg(rtv + static_cast<size_t>(rowmap(y)) * W + x);
     std::uint8_t out[3];
-    guide_pixel(rp, rq, __fdiv_rn(1.f, static_cast<float>(5 * k)),
-                blurred + (static_cast<size_t>(rowmap(my)) * W + mx) * 3,
-                blurred + (static_cast<size_t>(rowmap(y)) * W + x) * 3, out);
+    const float* gq = blurred + (static_cast<size_t>(rowmap(my)) * W + mx) * 3;
+    const float* gp = blurred + (static_cast<size_t>(rowmap(y)) * W + x) * 3;
+    const float bq[3] = {__ldg(gq), __ldg(gq + 1), __ldg(gq + 2)};
+    const float bp[3] = {__ldg(gp), __ldg(gp + 1), __ldg(gp + 2)};
+    guide_pixel(rp, rq, __fdiv_rn(1.f, static_cast<float>(5 * k)), bq, bp, out);
     std::uint8_t* g = guide + (static_cast<size_t>(y - dst_y0) * W + x) * 3;
     g[0] = out[0];
     g[1] = out[1];

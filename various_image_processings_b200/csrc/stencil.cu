@@ -3,9 +3,11 @@
 // (src/bilateral_filter_impl.cu:7-96, 98-202) and adaptive_bilateral_filter_kernel
 // (src/adaptive_bilateral_filter_impl.cu:7-115).  New design, no code shared with the reference:
 //
-//  * persistent CTAs (2 per SM, 256 threads) stride over 8P x 32 output tiles; a CTA stages the tile plus its
-//    radius halo ONCE as packed 32-bit pixels (B | G<<8 | R<<16; JBF: {guide, src} pairs) in shared memory,
-//    so a tap is one VABSDIFF4.U8.ACC instead of six byte loads and three abs;
+//  * one persistent CTA per SM of up to three 256-thread warp groups; every group has its own tile buffer and named
+//    barrier and pulls 8P x 32 output tiles from a counter in shared memory, all groups share one LUT.  A group stages
+//    its tile plus the radius halo ONCE as packed 32-bit pixels (B | G<<8 | R<<16; JBF: {guide, src} pairs), four
+//    pixels per thread from aligned 32-bit loads, so a tap is one VABSDIFF4.U8.ACC instead of six byte loads and
+//    three abs;
 //  * a lane owns one image ROW of the warp's P x 32 sub-tile and P horizontally adjacent outputs: with an odd
 //    tile pitch all 32 lanes hit distinct banks, and one neighbour load + unpack feeds up to P taps;
 //  * the range LUT is replicated 32x in shared memory (entry i of lane l at word 32*i + l) so the
