@@ -365,7 +365,8 @@ template <int K>
 struct GuideLayout {
     static constexpr int r = K / 2;
     static constexpr int MW = kTW + 2 * r, MH = kTH + 2 * r;
-    static constexpr int hs_off = (MW * MH * 4 + 15) & ~15;
+    static constexpr int TP = MW + 2;   // rtv tile pitch: consecutive rows 10 banks apart
+    static constexpr int hs_off = (TP * MH * 4 + 15) & ~15;
     static constexpr int out_off = hs_off + MH * kTW * 8;
     static constexpr int bl_off = (out_off + kTH * kTW * 3 + 15) & ~15;   // blurred tile + halo: MH x MW x 3 floats
     static constexpr int total = bl_off + MW * MH * 12;
@@ -413,7 +414,7 @@ __global__ void __launch_bounds__(kThreads, 3) guide_kernel(const float* __restr
         const int wrow = tid >> 5, lane_ = tid & 31;
         for (int ey = wrow; ey < L::MH; ey += kThreads / 32) {       // rtv: a warp per row
             const float* g = rtv + static_cast<size_t>(rowmap(Y0 - r + ey)) * W + (X0 - r);
-            for (int ex = lane_; ex < L::MW; ex += 32) cp_async4(tile + ey * L::MW + ex, g + ex);
+            for (int ex = lane_; ex < L::MW; ex += 32) cp_async4(tile + ey * L::TP + ex, g + ex);
         }
 #pragma unroll 4
         for (int ey = 0; ey < L::MH; ++ey) {                          // blurred: the CTA per row
@@ -425,7 +426,7 @@ __global__ void __launch_bounds__(kThreads, 3) guide_kernel(const float* __restr
         for (int e = tid; e < L::MW * L::MH; e += kThreads) {
             const int ey = e / L::MW, ex = e - ey * L::MW;
             const int gx = clampi(X0 - r + ex, 0, W - 1);
-            tile[e] = __ldg(rtv + static_cast<size_t>(rowmap(Y0 - r + ey)) * W + gx);
+            tile[ey * L::TP + ex] = __ldg(rtv + static_cast<size_t>(rowmap(Y0 - r + ey)) * W + gx);
         }
         for (int e = tid; e < L::MH * kRowF; e += kThreads) {
             const int ey = e / kRowF, t = e - ey * kRowF;
@@ -435,54 +436,87 @@ __global__ void __launch_bounds__(kThreads, 3) guide_kernel(const float* __restr
     }
     __syncthreads();
 
-    // horizontal pass: (min value, smallest kx attaining it); strict '>' keeps the first (:152-165)
-    for (int e = tid; e < L::MH * kTW; e += kThreads) {
-        const int row = e / kTW, col = e - row * kTW;
-        const float* tr = tile + row * L::MW + col;
-        float best = 1e10f;  // :152
-        int bj = -1;
+    // Both passes of the separable argmin use the same scheme: a thread holds the K+7 inputs of 8 adjacent outputs and
+    // builds "first minimum of a power-of-two block" by doubling -- the later half replaces the earlier one only when it is
+    // STRICTLY smaller, which is the reference's strict '>' scan (:152-165) made associative -- and a K-window is two
+    // overlapping blocks.  A window without any value below 1e10f keeps (1e10f, -1) like the reference's initial state.
+    constexpr int N = K + 7;
+    constexpr int Q = K >= 8 ? 8 : (K >= 4 ? 4 : (K >= 2 ? 2 : 1));
+    // horizontal pass: a thread = 8 adjacent columns of one row -> (min value, smallest kx attaining it)
+    for (int item = tid; item < L::MH * (kTW / 8); item += kThreads) {
+        const int cg = item & 7, row = item >> 3;
+        const float* tr = tile + row * L::TP + cg * 8;
+        float v[N];
+        int id[N];
 #pragma unroll
-        for (int j = 0; j < K; ++j) {
-            const float v = tr[j];
-            if (best > v) {
-                best = v;
-                bj = j;
+        for (int j = 0; j < N; ++j) {
+            v[j] = tr[j];
+            id[j] = j;
+        }
+#pragma unroll
+        for (int d = 1; d < Q; d <<= 1) {
+#pragma unroll
+            for (int j = 0; j + d < N; ++j) {
+                const bool take = v[j + d] < v[j];
+                v[j] = take ? v[j + d] : v[j];
+                id[j] = take ? id[j + d] : id[j];
             }
         }
-        hs[e] = make_float2(best, __int_as_float(bj));
+        float2* hrow = hs + row * kTW + cg * 8;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const bool take = v[i + K - Q] < v[i];
+            float best = take ? v[i + K - Q] : v[i];
+            int bj = (take ? id[i + K - Q] : id[i]) - i;
+            if (!(1e10f > best)) {  // :152
+                best = 1e10f;
+                bj = -1;
+            }
+            hrow[(i + cg) & 7] = make_float2(best, __int_as_float(bj));   // rotated: conflict-free 8-byte stores
+        }
     }
     __syncthreads();
 
+    // vertical pass: lane <-> column, 8 consecutive rows per thread -> smallest ky among equal row minima
     const int col = (warp & 1) * 32 + lane;
     const int r0 = (warp >> 1) * kRows;
-    const int x = min(X0 + col, W - 1);
     const float sigma_alpha = __fdiv_rn(1.f, static_cast<float>(5 * K));  // :121
     float best[kRows];
     int bj[kRows], bky[kRows];
+    {
+        static_assert(kRows == 8, "8 outputs per thread");
+        const int hcol = (col & ~7) + ((col + (col >> 3)) & 7);
+        float v[N];
+        int xj[N], yk[N];
 #pragma unroll
-    for (int i = 0; i < kRows; ++i) {
-        best[i] = 1e10f;
-        bj[i] = -1;
-        bky[i] = 0;
-    }
+        for (int R = 0; R < N; ++R) {
+            const float2 h = hs[(r0 + R) * kTW + hcol];
+            v[R] = h.x;
+            xj[R] = __float_as_int(h.y);
+            yk[R] = R;
+        }
 #pragma unroll
-    for (int R = 0; R < K + kRows - 1; ++R) {
-        const float2 h = hs[(r0 + R) * kTW + col];
+        for (int d = 1; d < Q; d <<= 1) {
+#pragma unroll
+            for (int R = 0; R + d < N; ++R) {
+                const bool take = v[R + d] < v[R];
+                v[R] = take ? v[R + d] : v[R];
+                xj[R] = take ? xj[R + d] : xj[R];
+                yk[R] = take ? yk[R + d] : yk[R];
+            }
+        }
 #pragma unroll
         for (int i = 0; i < kRows; ++i) {
-            if (R - i >= 0 && R - i < K) {
-                if (best[i] > h.x) {
-                    best[i] = h.x;
-                    bj[i] = __float_as_int(h.y);
-                    bky[i] = R - i;
-                }
-            }
+            const bool take = v[i + K - Q] < v[i];
+            best[i] = take ? v[i + K - Q] : v[i];
+            bj[i] = take ? xj[i + K - Q] : xj[i];
+            bky[i] = (take ? yk[i + K - Q] : yk[i]) - i;
         }
     }
 #pragma unroll
     for (int i = 0; i < kRows; ++i) {
         const int y = min(Y0 + r0 + i, H - 1);
-        const float rp = tile[(r0 + i + r) * L::MW + col + r];
+        const float rp = tile[(r0 + i + r) * L::TP + col + r];
         const float* bpp = bl + ((r0 + i + r) * L::MW + col + r) * 3;
         const float bp[3] = {bpp[0], bpp[1], bpp[2]};
         float rmin = best[i];
