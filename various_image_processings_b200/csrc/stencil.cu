@@ -316,7 +316,7 @@ __device__ __forceinline__ void do_row(int len, const typename Elem<MODE>::type*
 }
 
 struct SmemLayout {
-    int lut_off, w_off, hw_off, sched_off, tile_off, hs_off, total;   // tile_off / hs_off: group 0; group g adds g * group_stride
+    int lut_off, w_off, hw_off, sched_off, tile_off, hs_off, bs_off, total;   // tile_off / hs_off / bs_off: group 0; group g adds g * group_stride
     int tile_pitch, tile_w, tile_h, hs_pitch, w_pitch, group_stride;
 };
 
@@ -344,6 +344,9 @@ __host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, i
     L.hs_off = off;
     if (mode == kABF) off += L.hs_pitch * L.tile_h * 8;
     off = (off + 15) & ~15;
+    L.bs_off = off;  // ABF: k x k box sums of the tile's outputs, uint4 {B, G, R, -} per output
+    if (mode == kABF) off += L.hs_pitch * kTileRows * 16;
+    off = (off + 15) & ~15;
     L.group_stride = off - L.tile_off;
     L.total = L.tile_off + n_groups * L.group_stride;
     return L;
@@ -365,6 +368,7 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
     int* const sched = reinterpret_cast<int*>(smem + L.sched_off);
     E* const tile = reinterpret_cast<E*>(smem + L.tile_off + group * L.group_stride);
     uint2* const hs = reinterpret_cast<uint2*>(smem + L.hs_off + group * L.group_stride);
+    uint4* const bs = reinterpret_cast<uint4*>(smem + L.bs_off + group * L.group_stride);
 
     const int tid = threadIdx.x - group * kThreads;
     const int lane = tid & 31;
@@ -468,6 +472,31 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
                 }
             }
             group_sync();
+            // vertical k-sums of the horizontal sums: a thread owns one output column and kTileRows / nseg consecutive
+            // rows; the window slides down (add the entering row, subtract the leaving one) -- all exact integers
+            constexpr int ncols = kWarps * P, nseg = kThreads / ncols, rows_per = kTileRows / nseg;
+            static_assert(nseg * ncols == kThreads && rows_per * nseg == kTileRows, "column / segment split");
+            {
+                const int col = tid % ncols, y0 = (tid / ncols) * rows_per;
+                const uint2* hc = hs + y0 * L.hs_pitch + col;
+                std::uint32_t sb = 0, sg = 0, sr = 0;
+                for (int j = 0; j < k; ++j) {
+                    const uint2 hv = hc[j * L.hs_pitch];
+                    sb += hv.x & 0xffffu;
+                    sr += hv.x >> 16;
+                    sg += hv.y;
+                }
+                bs[y0 * L.hs_pitch + col] = make_uint4(sb, sg, sr, 0u);
+#pragma unroll
+                for (int y = 1; y < rows_per; ++y) {
+                    const uint2 hn = hc[(y + k - 1) * L.hs_pitch], ho = hc[(y - 1) * L.hs_pitch];
+                    sb += (hn.x & 0xffffu) - (ho.x & 0xffffu);
+                    sr += (hn.x >> 16) - (ho.x >> 16);
+                    sg += hn.y - ho.y;
+                    bs[(y0 + y) * L.hs_pitch + col] = make_uint4(sb, sg, sr, 0u);
+                }
+            }
+            group_sync();
         }
 
         Acc<MODE, P> A;
@@ -477,14 +506,8 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
 #pragma unroll
             for (int i = 0; i < P; ++i) {
                 const std::uint32_t c = tcentre[i];
-                std::uint32_t sb = 0, sg = 0, sr = 0;
-                const uint2* hcol = hs + lane * L.hs_pitch + warp * P + i;
-                for (int j = 0; j < k; ++j) {
-                    const uint2 hv = hcol[j * L.hs_pitch];
-                    sb += hv.x & 0xffffu;
-                    sr += hv.x >> 16;
-                    sg += hv.y;
-                }
+                const uint4 box = bs[lane * L.hs_pitch + warp * P + i];
+                const std::uint32_t sb = box.x, sg = box.y, sr = box.z;
                 const float kk = static_cast<float>(k * k);
                 const float c0 = static_cast<float>(c & 0xffu), c1 = static_cast<float>((c >> 8) & 0xffu),
                             c2 = static_cast<float>((c >> 16) & 0xffu);
