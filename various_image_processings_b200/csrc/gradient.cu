@@ -93,36 +93,50 @@ __device__ __forceinline__ int sq3(const std::uint32_t a, const std::uint32_t b)
     return __dp4a(d, d, 0u);
 }
 
+// A thread produces 4 columns x kFastRows rows: the kFastRows + 2 source rows it needs are read once as three aligned
+// words each and cut into pixels once; every row then serves as the upper, the centre and the lower neighbour.
+constexpr int kFastRows = 4;
 __global__ void __launch_bounds__(256) gradient_u8c3_fast_kernel(const std::uint8_t* __restrict__ src,
                                                                  float* __restrict__ dst, const int W, const int H,
                                                                  const int src_y0, const int src_rows, const int dst_y0,
                                                                  const int out_y0, const int out_rows) {
     const int x = 4 * (blockIdx.x * 32 + threadIdx.x);
-    const int y = out_y0 + blockIdx.y * 8 + threadIdx.y;
-    if (x >= W || y >= out_y0 + out_rows) return;
+    const int y0 = out_y0 + (blockIdx.y * 8 + threadIdx.y) * kFastRows;
+    if (x >= W || y0 >= out_y0 + out_rows) return;
     const int wpr = (W * 3) >> 2;  // words per row
     auto row_ptr = [&](int yy) {
         const int r = clampi(clampi(yy, 0, H - 1), src_y0, src_y0 + src_rows - 1) - src_y0;
         return reinterpret_cast<const std::uint32_t*>(src) + static_cast<size_t>(r) * wpr + (x >> 2) * 3;
     };
-    const std::uint32_t* m = row_ptr(y);
-    const std::uint32_t* u = row_ptr(y - 1);
-    const std::uint32_t* d = row_ptr(y + 1);
-    const std::uint32_t m0 = __ldg(m), m1 = __ldg(m + 1), m2 = __ldg(m + 2);
-    const std::uint32_t u0 = __ldg(u), u1 = __ldg(u + 1), u2 = __ldg(u + 2);
-    const std::uint32_t d0 = __ldg(d), d1 = __ldg(d + 1), d2 = __ldg(d + 2);
-    // pixels x .. x+3 of a row held in words w0 w1 w2 (12 bytes)
-    const std::uint32_t p0 = m0, p1 = __funnelshift_r(m0, m1, 24), p2 = __funnelshift_r(m1, m2, 16), p3 = m2 >> 8;
-    const std::uint32_t pm = x > 0 ? (__ldg(m - 1) >> 8) : p0;      // pixel x-1 (clamped)
-    const std::uint32_t pp = x + 4 < W ? __ldg(m + 3) : p3;          // pixel x+4 (clamped)
-    const std::uint32_t a0 = u0, a1 = __funnelshift_r(u0, u1, 24), a2 = __funnelshift_r(u1, u2, 16), a3 = u2 >> 8;
-    const std::uint32_t b0 = d0, b1 = __funnelshift_r(d0, d1, 24), b2 = __funnelshift_r(d1, d2, 16), b3 = d2 >> 8;
-    float4 o;
-    o.x = sqrtf(static_cast<float>(sq3(p1, pm) + sq3(b0, a0)));
-    o.y = sqrtf(static_cast<float>(sq3(p2, p0) + sq3(b1, a1)));
-    o.z = sqrtf(static_cast<float>(sq3(p3, p1) + sq3(b2, a2)));
-    o.w = sqrtf(static_cast<float>(sq3(pp, p2) + sq3(b3, a3)));
-    *reinterpret_cast<float4*>(dst + static_cast<size_t>(y - dst_y0) * W + x) = o;
+    // pixels x .. x+3 of rows y0-1 .. y0+kFastRows, plus pixel x-1 / x+4 of the centre rows (clamped)
+    std::uint32_t p[kFastRows + 2][4], pm[kFastRows], pp[kFastRows];
+#pragma unroll
+    for (int j = 0; j < kFastRows + 2; ++j) {
+        const std::uint32_t* m = row_ptr(y0 - 1 + j);
+        const std::uint32_t w0 = __ldg(m), w1 = __ldg(m + 1), w2 = __ldg(m + 2);
+        p[j][0] = w0;
+        p[j][1] = __funnelshift_r(w0, w1, 24);
+        p[j][2] = __funnelshift_r(w1, w2, 16);
+        p[j][3] = w2 >> 8;
+        if (j >= 1 && j <= kFastRows) {
+            pm[j - 1] = x > 0 ? (__ldg(m - 1) >> 8) : w0;
+            pp[j - 1] = x + 4 < W ? __ldg(m + 3) : p[j][3];
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < kFastRows; ++i) {
+        const int y = y0 + i;
+        if (y >= out_y0 + out_rows) break;
+        const std::uint32_t* c = p[i + 1];
+        const std::uint32_t* u = p[i];
+        const std::uint32_t* d = p[i + 2];
+        float4 o;
+        o.x = sqrtf(static_cast<float>(sq3(c[1], pm[i]) + sq3(d[0], u[0])));
+        o.y = sqrtf(static_cast<float>(sq3(c[2], c[0]) + sq3(d[1], u[1])));
+        o.z = sqrtf(static_cast<float>(sq3(c[3], c[1]) + sq3(d[2], u[2])));
+        o.w = sqrtf(static_cast<float>(sq3(pp[i], c[2]) + sq3(d[3], u[3])));
+        *reinterpret_cast<float4*>(dst + static_cast<size_t>(y - dst_y0) * W + x) = o;
+    }
 }
 
 // Generic channel count (u8) and float input: one thread per output pixel, clamped global reads.
@@ -170,7 +184,7 @@ cudaError_t launch_gradient_u8(const std::uint8_t* src, float* dst, int width, i
     if (channels == 3 && (width & 3) == 0 && (reinterpret_cast<std::uintptr_t>(src) & 3u) == 0 &&
         (reinterpret_cast<std::uintptr_t>(dst) & 15u) == 0) {
         const dim3 block(32, 8);
-        const dim3 grid((width / 4 + 31) / 32, (out_rows + 7) / 8);
+        const dim3 grid((width / 4 + 31) / 32, (out_rows + 8 * kFastRows - 1) / (8 * kFastRows));
         gradient_u8c3_fast_kernel<<<grid, block, 0, stream>>>(src, dst, width, height, src_y0, src_rows, dst_y0, out_y0,
                                                               out_rows);
     } else if (channels == 3 || channels == 1) {
