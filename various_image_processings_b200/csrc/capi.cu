@@ -50,7 +50,7 @@ struct StencilTables {
     int last_nz = 0;    // last non-zero entry of the colour table
     int device = 0, sm_count = 0;
     std::vector<float> h_ks, h_lut;
-    DeviceBuf d_lut, d_ksw, d_hw, d_ks;
+    DeviceBuf d_lut, d_hw, d_ks;
 };
 
 int validate(int width, int height, int ksize, float ss, float sc) {
@@ -108,25 +108,20 @@ int init_tables(StencilTables& T, int width, int height, int ksize, float ss, fl
     build_luts(ksize, ss, sc, table_len, lut_mode, T.h_ks, T.h_lut);
 
     const int r = T.radius;
-    std::vector<float> ksw(static_cast<size_t>(ksize) * (r + 1));
     std::vector<int> hw(ksize);
     for (int ky = -r; ky <= r; ky++) {
         int h = 0;
         while ((h + 1) * (h + 1) + ky * ky <= r * r) h++;
         hw[ky + r] = h;
-        for (int d = 0; d <= r; d++) ksw[(ky + r) * (r + 1) + d] = T.h_ks[(ky + r) * ksize + (d + r)];
     }
     // Trailing zeros of the colour table: every index > last_nz has weight exactly 0, so clamping the index
     // to last_nz+1 is bit-neutral and lets the 32x replicated table shrink (vip::stencil_pick_lut decides).
     T.last_nz = table_len - 1;
     while (T.last_nz > 0 && T.h_lut[T.last_nz] == 0.f) T.last_nz--;
     if ((e = T.d_lut.alloc(table_len * sizeof(float))) != cudaSuccess) return cu(e);
-    if ((e = T.d_ksw.alloc(ksw.size() * sizeof(float))) != cudaSuccess) return cu(e);
     if ((e = T.d_hw.alloc(hw.size() * sizeof(int))) != cudaSuccess) return cu(e);
     if ((e = T.d_ks.alloc(T.h_ks.size() * sizeof(float))) != cudaSuccess) return cu(e);
     if ((e = cudaMemcpy(T.d_lut.p, T.h_lut.data(), table_len * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess)
-        return cu(e);
-    if ((e = cudaMemcpy(T.d_ksw.p, ksw.data(), ksw.size() * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess)
         return cu(e);
     if ((e = cudaMemcpy(T.d_hw.p, hw.data(), hw.size() * sizeof(int), cudaMemcpyHostToDevice)) != cudaSuccess)
         return cu(e);
@@ -166,7 +161,6 @@ int run_stencil(const StencilTables& T, vip::StencilMode mode, const uint8_t* d_
     a.radius = T.radius;
     a.lut = static_cast<const float*>(T.d_lut.p);
     vip::stencil_pick_lut(mode, T.radius, T.table_len, T.last_nz, &a.lut_n, &a.lut_clamp);
-    a.ksw = static_cast<const float*>(T.d_ksw.p);
     a.hw = static_cast<const int*>(T.d_hw.p);
     a.ks_full = static_cast<const float*>(T.d_ks.p);
     return cu(vip::launch_stencil(mode, a, T.sm_count, static_cast<cudaStream_t>(stream)));

@@ -7,6 +7,10 @@
 //     iterate after every iteration: the receiving device's stream waits for the neighbour's "iteration done"
 //     event and then pulls the rows with cudaMemcpyPeerAsync (NVLink P2P when peer access is enabled), so the
 //     exchange is ordered by events only -- no host synchronisation inside the iteration loop;
+//   * every device slot has its own host worker thread that enqueues the slot's work (kernels, event records, peer
+//     copies): with one enqueueing thread the 8 x 3 x (3 launches + events + 2 peer copies) calls of a BTF run cost
+//     more host time than the GPUs need for the work.  Workers only order themselves through one atomic counter per
+//     slot ("my iteration-done event has been recorded"), which the neighbours poll before cudaStreamWaitEvent;
 //   * frame batches are dealt round-robin to the devices, two in-flight slots per device so that the upload of
 //     frame i+1 and the download of frame i-1 overlap the kernels of frame i; no inter-device traffic.
 // The same device id may appear several times in the list ("virtual" devices): the strip logic is then
@@ -14,7 +18,13 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
+#include <climits>
+#include <condition_variable>
+#include <memory>
+#include <mutex>
 #include <new>
+#include <thread>
 #include <vector>
 
 #include "../../include/vip_c_api.h"
@@ -48,12 +58,23 @@ struct Slot {
 
 }  // namespace
 
+struct Worker {
+    std::thread th;
+    std::mutex mu;
+    std::condition_variable cv;
+    int cmd_gen = 0, done_gen = 0;  // a run is requested by cmd_gen++, finished when done_gen == cmd_gen
+    bool quit = false;
+    int rc = VIP_OK;
+};
+
 struct vip_mg {
     int n = 0, kind = 0, width = 0, height = 0, ksize = 0, nitr = 0, halo = 0;
     float ss = 0.f, sc = 0.f;
     int result_buf = 0;  // BTF: which of buf[0/1] holds the final iterate (-1: src)
     bool batch_ready = false;
     std::vector<Slot> slots;
+    std::vector<std::unique_ptr<Worker>> workers;          // one enqueueing thread per slot
+    std::unique_ptr<std::atomic<int>[]> iter_recorded;     // BTF: iterations whose "done" event slot i has recorded
 };
 
 namespace {
@@ -91,6 +112,101 @@ int run_one(vip_mg* m, Slot& s, const uint8_t* src, uint8_t* dst, const vip_stri
         case VIP_MG_ABF: return vip_abf_run_strip(s.abf, src, dst, &st, s.stream);
         default: return VIP_E_UNSUPPORTED;
     }
+}
+
+// Everything slot i contributes to one run, enqueued on its stream by its worker thread.
+int enqueue_slot(vip_mg* m, int i) {
+    Slot& s = m->slots[i];
+    const size_t row_bytes = static_cast<size_t>(m->width) * 3;
+    cudaError_t e;
+    if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
+    if ((e = cudaEventRecord(s.ev_start, s.stream)) != cudaSuccess) return cu(e);
+    if (m->kind != VIP_MG_BTF) {
+        const vip_strip st{s.sy0, s.srows, s.y0, s.y0, s.rows};
+        const int rc = run_one(m, s, s.src, s.buf[0], st);
+        if (rc != VIP_OK) return rc;
+    } else {
+        auto wait_recorded = [&](int j, int want) {  // the neighbour's event must be RECORDED before it can be waited on
+            while (m->iter_recorded[j].load(std::memory_order_acquire) < want) std::this_thread::yield();
+        };
+        for (int it = 0; it < m->nitr; it++) {
+            const int ob = it & 1;
+            const uint8_t* in = (it == 0) ? s.src : s.buf[ob ^ 1];
+            const vip_strip st{s.sy0, s.srows, s.sy0, s.y0, s.rows};
+            const int rc = vip_btf_iterate_strip(s.btf, in, s.buf[ob], &st, s.stream);
+            if (rc != VIP_OK) return rc;
+            if ((e = cudaEventRecord(s.ev_iter[it], s.stream)) != cudaSuccess) return cu(e);
+            m->iter_recorded[i].store(it + 1, std::memory_order_release);
+            if (it + 1 < m->nitr) {
+                // halo refresh of the new iterate: pull the rows [sy0, y0) from the slot above and
+                // [y0+rows, sy0+srows) from the slot below, on the RECEIVER's stream
+                if (i > 0 && s.y0 > s.sy0) {
+                    Slot& up = m->slots[i - 1];
+                    wait_recorded(i - 1, it + 1);
+                    if ((e = cudaStreamWaitEvent(s.stream, up.ev_iter[it], 0)) != cudaSuccess) return cu(e);
+                    e = cudaMemcpyPeerAsync(s.buf[ob], s.device, up.buf[ob] + row_bytes * (s.sy0 - up.sy0), up.device,
+                                            row_bytes * (s.y0 - s.sy0), s.stream);
+                    if (e != cudaSuccess) return cu(e);
+                }
+                const int below0 = s.y0 + s.rows, below1 = s.sy0 + s.srows;
+                if (i + 1 < m->n && below1 > below0) {
+                    Slot& dn = m->slots[i + 1];
+                    wait_recorded(i + 1, it + 1);
+                    if ((e = cudaStreamWaitEvent(s.stream, dn.ev_iter[it], 0)) != cudaSuccess) return cu(e);
+                    e = cudaMemcpyPeerAsync(s.buf[ob] + row_bytes * (below0 - s.sy0), s.device,
+                                            dn.buf[ob] + row_bytes * (below0 - dn.sy0), dn.device,
+                                            row_bytes * (below1 - below0), s.stream);
+                    if (e != cudaSuccess) return cu(e);
+                }
+            }
+        }
+    }
+    if ((e = cudaEventRecord(s.ev_stop, s.stream)) != cudaSuccess) return cu(e);
+    return VIP_OK;
+}
+
+void worker_main(vip_mg* m, int i) {
+    Worker& w = *m->workers[i];
+    for (;;) {
+        int gen;
+        {
+            std::unique_lock<std::mutex> lock(w.mu);
+            w.cv.wait(lock, [&] { return w.quit || w.cmd_gen != w.done_gen; });
+            if (w.quit) return;
+            gen = w.cmd_gen;
+        }
+        const int rc = enqueue_slot(m, i);
+        if (rc != VIP_OK) m->iter_recorded[i].store(INT_MAX, std::memory_order_release);  // never block the neighbours
+        {
+            std::lock_guard<std::mutex> lock(w.mu);
+            w.rc = rc;
+            w.done_gen = gen;
+        }
+        w.cv.notify_all();
+    }
+}
+
+// Blocks until every worker has finished ENQUEUEING the current run; returns the first error.
+int wait_workers(vip_mg* m) {
+    int rc = VIP_OK;
+    for (auto& wp : m->workers) {
+        std::unique_lock<std::mutex> lock(wp->mu);
+        wp->cv.wait(lock, [&] { return wp->cmd_gen == wp->done_gen; });
+        if (rc == VIP_OK) rc = wp->rc;
+    }
+    return rc;
+}
+
+void stop_workers(vip_mg* m) {
+    for (auto& wp : m->workers) {
+        {
+            std::lock_guard<std::mutex> lock(wp->mu);
+            wp->quit = true;
+        }
+        wp->cv.notify_all();
+        if (wp->th.joinable()) wp->th.join();
+    }
+    m->workers.clear();
 }
 
 }  // namespace
@@ -170,6 +286,16 @@ int vip_mg_create(vip_mg** out, const int* device_ids, int n_devices, int kind, 
         vip_mg_destroy(m);
         return rc;
     }
+    m->iter_recorded.reset(new (std::nothrow) std::atomic<int>[n_devices]);
+    if (!m->iter_recorded) {
+        vip_mg_destroy(m);
+        return VIP_E_ALLOC;
+    }
+    for (int i = 0; i < n_devices; i++) m->iter_recorded[i].store(0);
+    for (int i = 0; i < n_devices; i++) {
+        m->workers.emplace_back(new Worker());
+        m->workers.back()->th = std::thread(worker_main, m, i);
+    }
     *out = m;
     return VIP_OK;
 }
@@ -177,6 +303,8 @@ int vip_mg_create(vip_mg** out, const int* device_ids, int n_devices, int kind, 
 int vip_mg_destroy(vip_mg* m) {
     if (!m) return VIP_OK;
     DeviceGuard guard;
+    wait_workers(m);
+    stop_workers(m);
     for (Slot& s : m->slots) free_slot(m, s);
     delete m;
     return VIP_OK;
@@ -192,6 +320,7 @@ int vip_mg_strip_rows(const vip_mg* m, int i, int* y0, int* rows) {
 
 int vip_mg_scatter_host(vip_mg* m, const uint8_t* h_src) {
     if (!m || !h_src) return VIP_E_NULL;
+    wait_workers(m);
     DeviceGuard guard;
     const size_t row_bytes = static_cast<size_t>(m->width) * 3;
     for (Slot& s : m->slots) {
@@ -205,6 +334,7 @@ int vip_mg_scatter_host(vip_mg* m, const uint8_t* h_src) {
 
 int vip_mg_scatter_device(vip_mg* m, const uint8_t* d_src_on_dev0) {
     if (!m || !d_src_on_dev0) return VIP_E_NULL;
+    wait_workers(m);
     DeviceGuard guard;
     const size_t row_bytes = static_cast<size_t>(m->width) * 3;
     const int dev0 = m->slots[0].device;
@@ -219,68 +349,24 @@ int vip_mg_scatter_device(vip_mg* m, const uint8_t* d_src_on_dev0) {
 
 int vip_mg_run_async(vip_mg* m) {
     if (!m) return VIP_E_NULL;
-    DeviceGuard guard;
-    const size_t row_bytes = static_cast<size_t>(m->width) * 3;
-    cudaError_t e;
-    for (Slot& s : m->slots) {
-        if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
-        if ((e = cudaEventRecord(s.ev_start, s.stream)) != cudaSuccess) return cu(e);
-    }
-    if (m->kind != VIP_MG_BTF) {
-        for (Slot& s : m->slots) {
-            if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
-            const vip_strip st{s.sy0, s.srows, s.y0, s.y0, s.rows};
-            const int rc = run_one(m, s, s.src, s.buf[0], st);
-            if (rc != VIP_OK) return rc;
+    const int rc = wait_workers(m);  // a previous run still being enqueued
+    if (rc != VIP_OK) return rc;
+    for (int i = 0; i < m->n; i++) m->iter_recorded[i].store(0, std::memory_order_release);
+    if (m->kind == VIP_MG_BTF) m->result_buf = m->nitr > 0 ? ((m->nitr - 1) & 1) : -1;
+    for (auto& wp : m->workers) {
+        {
+            std::lock_guard<std::mutex> lock(wp->mu);
+            wp->cmd_gen++;
         }
-    } else {
-        m->result_buf = -1;
-        for (int it = 0; it < m->nitr; it++) {
-            const int ob = it & 1;
-            for (Slot& s : m->slots) {
-                if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
-                const uint8_t* in = (it == 0) ? s.src : s.buf[ob ^ 1];
-                const vip_strip st{s.sy0, s.srows, s.sy0, s.y0, s.rows};
-                const int rc = vip_btf_iterate_strip(s.btf, in, s.buf[ob], &st, s.stream);
-                if (rc != VIP_OK) return rc;
-                if ((e = cudaEventRecord(s.ev_iter[it], s.stream)) != cudaSuccess) return cu(e);
-            }
-            if (it + 1 < m->nitr) {
-                // halo refresh of the new iterate: pull the rows [sy0, y0) from the slot above and
-                // [y0+rows, sy0+srows) from the slot below, on the RECEIVER's stream
-                for (int i = 0; i < m->n; i++) {
-                    Slot& s = m->slots[i];
-                    if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
-                    if (i > 0 && s.y0 > s.sy0) {
-                        Slot& up = m->slots[i - 1];
-                        if ((e = cudaStreamWaitEvent(s.stream, up.ev_iter[it], 0)) != cudaSuccess) return cu(e);
-                        e = cudaMemcpyPeerAsync(s.buf[ob], s.device, up.buf[ob] + row_bytes * (s.sy0 - up.sy0), up.device,
-                                                row_bytes * (s.y0 - s.sy0), s.stream);
-                        if (e != cudaSuccess) return cu(e);
-                    }
-                    const int below0 = s.y0 + s.rows, below1 = s.sy0 + s.srows;
-                    if (i + 1 < m->n && below1 > below0) {
-                        Slot& dn = m->slots[i + 1];
-                        if ((e = cudaStreamWaitEvent(s.stream, dn.ev_iter[it], 0)) != cudaSuccess) return cu(e);
-                        e = cudaMemcpyPeerAsync(s.buf[ob] + row_bytes * (below0 - s.sy0), s.device,
-                                                dn.buf[ob] + row_bytes * (below0 - dn.sy0), dn.device,
-                                                row_bytes * (below1 - below0), s.stream);
-                        if (e != cudaSuccess) return cu(e);
-                    }
-                }
-            }
-            m->result_buf = ob;
-        }
-    }
-    for (Slot& s : m->slots) {
-        if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
-        if ((e = cudaEventRecord(s.ev_stop, s.stream)) != cudaSuccess) return cu(e);
+        wp->cv.notify_all();
     }
     return VIP_OK;
 }
 
 int vip_mg_wait(vip_mg* m) {
     if (!m) return VIP_E_NULL;
+    const int rc = wait_workers(m);
+    if (rc != VIP_OK) return rc;
     DeviceGuard guard;
     for (Slot& s : m->slots) {
         cudaError_t e = cudaSetDevice(s.device);
@@ -298,6 +384,8 @@ int vip_mg_run(vip_mg* m) {
 
 int vip_mg_gather_host(vip_mg* m, uint8_t* h_dst) {
     if (!m || !h_dst) return VIP_E_NULL;
+    const int wrc = wait_workers(m);
+    if (wrc != VIP_OK) return wrc;
     DeviceGuard guard;
     const size_t row_bytes = static_cast<size_t>(m->width) * 3;
     for (Slot& s : m->slots) {
@@ -315,6 +403,7 @@ int vip_mg_gather_host(vip_mg* m, uint8_t* h_dst) {
 
 int vip_mg_last_run_ms(const vip_mg* m, float* ms) {
     if (!m || !ms) return VIP_E_NULL;
+    wait_workers(const_cast<vip_mg*>(m));
     DeviceGuard guard;
     float worst = 0.f;
     for (const Slot& s : m->slots) {
@@ -332,6 +421,7 @@ int vip_mg_last_run_ms(const vip_mg* m, float* ms) {
 int vip_mg_run_batch_host(vip_mg* m, const uint8_t* h_src, uint8_t* h_dst, int n_frames) {
     if (!m || !h_src || !h_dst) return VIP_E_NULL;
     if (n_frames < 0) return VIP_E_SIZE;
+    wait_workers(m);
     DeviceGuard guard;
     const size_t frame_bytes = static_cast<size_t>(m->width) * m->height * 3;
     cudaError_t e;

@@ -26,9 +26,8 @@ struct StencilArgs {
     const float* lut;           // device: colour table (768 or 1536 floats)
     int lut_n;                  // entries replicated into shared memory
     int lut_clamp;              // 1: index is clamped to lut_n-1 (whose entry, and all after it, is 0)
-    const float* ksw;           // device: (2r+1) x (r+1) half rows of the spatial kernel, ksw[(ky+r)*(r+1)+|kx|]
     const int* hw;              // device: 2r+1 half widths, hw[ky+r] = floor(sqrt(r^2-ky^2))
-    const float* ks_full;       // device: ksize*ksize spatial kernel (generic fallback)
+    const float* ks_full;       // device: ksize*ksize spatial kernel (row ky: its 2*hw+1 non-zero weights are copied to shared memory)
 };
 
 cudaError_t launch_stencil(StencilMode mode, const StencilArgs& a, int sm_count, cudaStream_t stream);
