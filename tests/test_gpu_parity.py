@@ -491,6 +491,18 @@ def test_multigpu_driver_virtual_devices(vip, kind, k, n):
     assert mg.last_run_ms() > 0
 
 
+def test_multigpu_driver_many_slots_create_destroy(vip):
+    """8 slots (the 8 x B200 box) on whatever devices exist: the worker threads start / stop cleanly, repeatedly."""
+    n = torch.cuda.device_count()
+    w, h = 128, 8 * 40
+    img = O.rand_image(w, h, seed=3)
+    want = run_abf(vip, img, 9)
+    for rep in range(6):
+        mg = vip.MultiGpuFilter([i % n for i in range(8)], "abf", w, h, ksize=9)
+        assert np.array_equal(mg.execute(img), want)
+        del mg
+
+
 def test_multigpu_driver_real_devices(vip):
     n = torch.cuda.device_count()
     if n < 2:

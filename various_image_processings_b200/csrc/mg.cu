@@ -165,8 +165,8 @@ int enqueue_slot(vip_mg* m, int i) {
     return VIP_OK;
 }
 
-void worker_main(vip_mg* m, int i) {
-    Worker& w = *m->workers[i];
+void worker_main(vip_mg* m, Worker* wp, int i) {
+    Worker& w = *wp;
     for (;;) {
         int gen;
         {
@@ -292,10 +292,9 @@ int vip_mg_create(vip_mg** out, const int* device_ids, int n_devices, int kind, 
         return VIP_E_ALLOC;
     }
     for (int i = 0; i < n_devices; i++) m->iter_recorded[i].store(0);
-    for (int i = 0; i < n_devices; i++) {
-        m->workers.emplace_back(new Worker());
-        m->workers.back()->th = std::thread(worker_main, m, i);
-    }
+    // all Worker objects exist before the first thread starts: a running worker reads m->workers[i]
+    for (int i = 0; i < n_devices; i++) m->workers.emplace_back(new Worker());
+    for (int i = 0; i < n_devices; i++) m->workers[i]->th = std::thread(worker_main, m, m->workers[i].get(), i);
     *out = m;
     return VIP_OK;
 }
