@@ -358,12 +358,12 @@ def main():
     if filt in ("btf", "all"):
         alg_bytes = local_pixels * 9.0                    # dominant kernel = joint bilateral: src + guide in, dst out
         kernel_ms = None                                  # several kernels per step: see profiles/ for the split
-        instr_per_tap = 9.7
+        instr_per_tap = 8.5                               # JBF 17x17: smsp__inst_executed x 32 / taps (ncu, profiles/r01d)
         taps_per_px = taps * nitr + (2 * mask_taps(radius) if filt == "all" else 0)
     else:
         alg_bytes = local_pixels * 6.0                    # 3 B in + 3 B out per pixel
         kernel_ms = ms_step
-        instr_per_tap = 17.9 if filt == "abf" else 8.9
+        instr_per_tap = 18.1 if filt == "abf" else 7.8   # whole-kernel SASS instructions per tap measured by ncu (profiles/r01d; tile staging, box sums and epilogue included)
         taps_per_px = taps
     traffic = None
     try:
@@ -386,7 +386,7 @@ def main():
     issue = {"taps_per_pixel": taps_per_px, "gtaps_per_s": taps_s / 1e9, "est_instr_per_tap": instr_per_tap,
              "est_issue_util": taps_s * instr_per_tap / issue_peak, "sm_mhz_used": sm_mhz,
              "peak_thread_instr_per_s": issue_peak,
-             "note": "estimate = taps/s x SASS instructions per tap (DESIGN.md) / (SMs x 4 x 32 x clock); ncu's smsp__issue_active in profiles/ is the measurement"}
+             "note": "taps/s x SASS instructions per tap (ncu smsp__inst_executed of the same kernel, profiles/) / (SMs x 4 x 32 x clock); packed fp32x2 instructions count once here but hold the dispatch port twice, see DESIGN.md 3"}
 
     cpu = None
     if not args.no_cpu_baseline:
