@@ -196,6 +196,15 @@ def test_abf_radii(vip, k):
     assert np.array_equal(run_abf(vip, img, k), O.o_abf(img, k))
 
 
+@pytest.mark.parametrize("k,sc", [(11, 106.0), (15, 60.0), (15, 200.0), (31, 100.0), (31, 400.0), (3, 1000.0)])
+def test_abf_wide_sigma_color(vip, k, sc):
+    """A wide sigma_color leaves (almost) all 1536 entries of the ABF range table non-zero: 32 copies of it no longer fit
+    in shared memory, the kernel then runs with the 8x replicated table (stencil.cu, kLutNarrow).  Found by
+    tests/test_gpu_property.py (k=11, sigma_color=106 used to fail with an invalid launch configuration)."""
+    for img in (O.rand_image(150, 70, seed=int(sc)), (O.rand_image(97, 33, seed=k) // 255) * 255):
+        assert np.array_equal(run_abf(vip, img, k, 10.0, sc), O.o_abf(img, k, 10.0, sc))
+
+
 # ------------------------------------------------------------------ gradient (test/gradient.cu)
 @pytest.mark.parametrize("ch", [1, 2, 3])
 @pytest.mark.parametrize("w,h", [(50, 50), (1, 1), (2, 9), (1030, 21), (4100, 3)])

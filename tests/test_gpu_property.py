@@ -1,0 +1,120 @@
+"""Property-based GPU parity (hypothesis): random sizes, window sizes, sigmas, content classes and strip splits, every case
+bit-exact against the oracle in CUDA arithmetic (oracle/vip_oracle.c) through the C ABI.  Sizes stay small enough for the
+scalar oracle; the fixed-size / full-size cases live in test_gpu_parity.py."""
+import numpy as np
+import pytest
+
+import _oracle as O
+
+torch = pytest.importorskip("torch")
+hyp = pytest.importorskip("hypothesis")
+from hypothesis import HealthCheck, given, settings, strategies as st  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+SET = dict(max_examples=25, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow])
+
+
+@pytest.fixture(scope="module")
+def vip():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import various_image_processings_b200 as v
+    torch.cuda.set_device(0)
+    return v
+
+
+def make_image(w, h, kind, seed):
+    rs = np.random.RandomState(seed)
+    if kind == "rand":
+        return rs.randint(0, 256, size=(h, w, 3)).astype(np.uint8)
+    if kind == "narrow":                                   # the reference benchmark's content (sample/benchmark/main.cpp:213)
+        return rs.randint(100, 120, size=(h, w, 3)).astype(np.uint8)
+    if kind == "const":
+        return np.full((h, w, 3), rs.randint(0, 256), np.uint8)
+    if kind == "extreme":                                  # only 0 and 255: largest colour distances, ABF index up to 1530
+        return (rs.randint(0, 2, size=(h, w, 3)) * 255).astype(np.uint8)
+    return O.smooth_image(w, h, seed=seed)
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+sizes = st.tuples(st.integers(1, 150), st.integers(1, 90))
+kinds = st.sampled_from(["rand", "narrow", "const", "extreme", "smooth"])
+odd_k = st.integers(0, 10).map(lambda r: 2 * r + 1)
+sigma = st.floats(0.5, 200.0, allow_nan=False, allow_infinity=False, width=32)
+
+
+@settings(**SET)
+@given(wh=sizes, k=odd_k, ss=sigma, sc=sigma, kind=kinds, seed=st.integers(0, 10**6))
+def test_bf_jbf_random_cases(vip, wh, k, ss, sc, kind, seed):
+    w, h = wh
+    img, guide = make_image(w, h, kind, seed), make_image(w, h, "smooth", seed + 1)
+    d = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    f = vip.CudaBilateralFilter(w, h, k, ss, sc)
+    f.bilateral_filter(dev(img), d)
+    assert np.array_equal(d.cpu().numpy(), O.o_bf(img, k, ss, sc))
+    f.joint_bilateral_filter(dev(img), dev(guide), d)
+    assert np.array_equal(d.cpu().numpy(), O.o_jbf(img, guide, k, ss, sc))
+
+
+@settings(**SET)
+@given(wh=sizes, k=odd_k, ss=sigma, sc=sigma, kind=kinds, seed=st.integers(0, 10**6))
+def test_abf_random_cases(vip, wh, k, ss, sc, kind, seed):
+    w, h = wh
+    img = make_image(w, h, kind, seed)
+    d = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    vip.CudaAdaptiveBilateralFilter(w, h, k, ss, sc).execute(dev(img), d)
+    assert np.array_equal(d.cpu().numpy(), O.o_abf(img, k, ss, sc))
+
+
+@settings(max_examples=12, deadline=None, suppress_health_check=SET["suppress_health_check"])
+@given(wh=st.tuples(st.integers(20, 120), st.integers(40, 90)), k=st.sampled_from([3, 5, 9]), nitr=st.integers(1, 3),
+       kind=st.sampled_from(["rand", "narrow", "smooth"]), seed=st.integers(0, 10**6))
+def test_btf_stages_random_cases(vip, wh, k, nitr, kind, seed):
+    """blur / mRTV and guide stages exact (integer + ordered-float arithmetic); the end-to-end filter equals the oracle
+    except where device expf differs from glibc expf by one level of the guide: bounded."""
+    w, h = wh
+    img = make_image(w, h, kind, seed)
+    f = vip.CudaBilateralTextureFilter(w, h, k, nitr)
+    mag = O.o_gradient(img)
+    bl = torch.empty((h, w, 3), dtype=torch.float32, device="cuda")
+    rt = torch.empty((h, w), dtype=torch.float32, device="cuda")
+    f.compute_blur_and_rtv(dev(img), dev(mag), bl, rt)
+    torch.cuda.synchronize()
+    obl, ort = O.o_blur_rtv(img, mag, k)
+    assert np.array_equal(bl.cpu().numpy(), obl) and np.array_equal(rt.cpu().numpy(), ort)
+    g = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    f.compute_guide(bl, rt, g)
+    torch.cuda.synchronize()
+    og = O.o_guide(obl, ort, k)
+    dg = np.abs(g.cpu().numpy().astype(int) - og.astype(int))
+    assert dg.max() <= 1 and (dg != 0).mean() < 1e-3            # argmin exact; alpha blend within one expf ulp
+    d = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    f.execute(dev(img), d)
+    want = O.o_btf(img, k, nitr)
+    got = d.cpu().numpy()
+    assert (got != want).mean() < 5e-3
+
+
+@settings(max_examples=15, deadline=None, suppress_health_check=SET["suppress_health_check"])
+@given(w=st.integers(8, 140), h=st.integers(30, 120), k=st.sampled_from([3, 9, 15]), cut=st.floats(0.05, 0.95),
+       kind=st.sampled_from(["bf", "abf"]), seed=st.integers(0, 10**6))
+def test_two_strips_equal_whole_image(vip, w, h, k, cut, kind, seed):
+    """Any split into two row strips with radius-deep halos reproduces the whole-image result bit for bit."""
+    img = make_image(w, h, "rand", seed)
+    r = k // 2
+    y_cut = min(max(int(h * cut), 1), h - 1)
+    F = vip.CudaBilateralFilter(w, h, k) if kind == "bf" else vip.CudaAdaptiveBilateralFilter(w, h, k)
+    whole = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    (F.bilateral_filter if kind == "bf" else F.execute)(dev(img), whole)
+    out = np.empty_like(img)
+    for y0, y1 in ((0, y_cut), (y_cut, h)):
+        s0, s1 = max(0, y0 - r), min(h, y1 + r)
+        d = torch.empty((y1 - y0, w, 3), dtype=torch.uint8, device="cuda")
+        strip = vip.Strip(s0, s1 - s0, y0, y0, y1 - y0)
+        (F.bilateral_filter_strip if kind == "bf" else F.execute_strip)(dev(img[s0:s1]), d, strip)
+        torch.cuda.synchronize()
+        out[y0:y1] = d.cpu().numpy()
+    assert np.array_equal(out, whole.cpu().numpy())

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Developer loop on the GPU box: time each kernel of the hot path at BASELINE sizes and check it bit-for-bit against
 the reference's own CUDA kernels (oracle/_ref/libvip_ref_cuda.so -- checker only) on the same random input.
-  python tools/kbench.py [bf:3840x2160:11 abf:3840x2160:15 jbf:3840x2160:17 btf:3840x2160:9 ...]
+  python tools/kbench.py [bf:3840x2160:11 abf:3840x2160:15:10:100 abf:3840x2160:15 jbf:3840x2160:17 btf:3840x2160:9 ...]
 """
 import os
 import sys
@@ -39,7 +39,8 @@ def main():
     R = O.ref_cuda() if O.have_ref_cuda() else None
     content = os.environ.get("KB_CONTENT", "rand")
     for spec in (sys.argv[1:] or DEFAULT):
-        kind, size, k = spec.split(":")
+        kind, size, k, *sig = spec.split(":")          # optional sigma_space, sigma_color after the window size
+        ss, sc = (float(sig[0]), float(sig[1])) if len(sig) == 2 else (10.0, 30.0)
         w, h = map(int, size.split("x"))
         k = int(k)
         rs = np.random.RandomState(42)
@@ -79,18 +80,18 @@ def main():
             print(f"{spec:22s} {ms:8.3f} ms  {w * h / ms / 1e3:9.0f} Mpix/s  {nbytes / ms / 1e6:8.1f} GB/s algorithmic  {same}", flush=True)
             continue
         if kind in ("bf", "jbf"):
-            f = vip.CudaBilateralFilter(w, h, k)
+            f = vip.CudaBilateralFilter(w, h, k, ss, sc)
             run = (lambda: f.bilateral_filter_async(d_src, d_dst)) if kind == "bf" else (lambda: f.joint_bilateral_filter_async(d_src, d_guide, d_dst))
             t_per_px = taps(k // 2)
             if R:
-                p = R.refcu_bf_create(w, h, k, 10.0, 30.0)
+                p = R.refcu_bf_create(w, h, k, ss, sc)
                 rr = (lambda: R.refcu_bf_run(p, d_src.data_ptr(), d_ref.data_ptr())) if kind == "bf" else (lambda: R.refcu_jbf_run(p, d_src.data_ptr(), d_guide.data_ptr(), d_ref.data_ptr()))
         elif kind == "abf":
-            f = vip.CudaAdaptiveBilateralFilter(w, h, k)
+            f = vip.CudaAdaptiveBilateralFilter(w, h, k, ss, sc)
             run = lambda: f.execute_async(d_src, d_dst)
             t_per_px = taps(k // 2)
             if R:
-                p = R.refcu_abf_create(w, h, k, 10.0, 30.0)
+                p = R.refcu_abf_create(w, h, k, ss, sc)
                 rr = lambda: R.refcu_abf_run(p, d_src.data_ptr(), d_ref.data_ptr())
         else:
             f = vip.CudaBilateralTextureFilter(w, h, k, 3)

@@ -160,7 +160,7 @@ int run_stencil(const StencilTables& T, vip::StencilMode mode, const uint8_t* d_
     a.out_rows = s.out_rows;
     a.radius = T.radius;
     a.lut = static_cast<const float*>(T.d_lut.p);
-    vip::stencil_pick_lut(mode, T.radius, T.table_len, T.last_nz, &a.lut_n, &a.lut_clamp);
+    vip::stencil_pick_lut(mode, T.radius, T.table_len, T.last_nz, &a.lut_n, &a.lut_kind);
     a.hw = static_cast<const int*>(T.d_hw.p);
     a.ks_full = static_cast<const float*>(T.d_ks.p);
     return cu(vip::launch_stencil(mode, a, T.sm_count, static_cast<cudaStream_t>(stream)));

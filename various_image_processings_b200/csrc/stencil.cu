@@ -120,6 +120,18 @@ __device__ __forceinline__ void load_packed4(const std::uint8_t* __restrict__ p,
     out[3] = v2 >> 8;
 }
 
+// How the range table sits in shared memory (template parameter LK of the kernels):
+//   kLutFull     every entry 32 times (128 B): lane l reads copy l, any 32 indices are conflict-free; index not clamped
+//   kLutClamp    same, index clamped to lut_n-1 (a zero entry standing for the cut all-zero tail)
+//   kLutNarrow   every entry 8 times (32 B), clamped: for tables too long for 32 copies next to the tile buffers (ABF
+//                with a wide sigma_color: 1536 entries x 128 B = 192 KB); lanes l and l+8k share a copy, so two
+//                different indices can meet in a bank (<= 4-way, ~1.5 on average) -- only the LDS of the tap replays
+enum LutKind { kLutFull = 0, kLutClamp = 1, kLutNarrow = 2 };
+__host__ __device__ constexpr bool lut_clamped(const int lk) { return lk != kLutFull; }
+__host__ __device__ constexpr int lut_shift(const int lk) { return lk == kLutNarrow ? 5 : 7; }  // log2(bytes per entry)
+// bits(2^23 + i) << shift, modulo 2^32, for i = 0: what abf_weight's shifted float bits carry on top of (i << shift)
+__host__ __device__ constexpr std::uint32_t abf_index_bias(const int lk) { return 0x4b000000u << lut_shift(lk); }
+
 __device__ __forceinline__ float lds_f32(const std::uint32_t addr) {
     float v;
     asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
@@ -136,7 +148,7 @@ __device__ __forceinline__ float byte_to_float(const std::uint32_t v) {
 // A run of L consecutive taps (kx0 .. kx0+L-1) of one window row for the P outputs of this thread.
 // t points at the tile element of (first output, kx0); wp at the L weights of the run (16-byte aligned,
 // readable up to the next multiple of 4).  Per accumulator the taps are visited in increasing kx.
-template <int MODE, int P, int L, bool CLAMP>
+template <int MODE, int P, int L, int LK>
 __device__ __forceinline__ void run_taps(const typename Elem<MODE>::type* __restrict__ t, const float* __restrict__ wp,
                                          const std::uint32_t lut_addr, const std::uint32_t clamp_i, const float clamp_f,
                                          Acc<MODE, P>& A) {
@@ -152,8 +164,8 @@ __device__ __forceinline__ void run_taps(const typename Elem<MODE>::type* __rest
     const unsigned long long one2 = pack2(1.f, 1.f);
     auto weight = [&](const std::uint32_t q, const std::uint32_t c, const float ks) {
         std::uint32_t sad = __vsadu4(q, c);
-        if constexpr (CLAMP) sad = min(sad, clamp_i);
-        return __fmul_rn(ks, lds_f32(lut_addr + (sad << 7)));
+        if constexpr (lut_clamped(LK)) sad = min(sad, clamp_i);
+        return __fmul_rn(ks, lds_f32(lut_addr + (sad << lut_shift(LK))));
     };
 #pragma unroll
     for (int n = 0; n < P + L - 1; ++n) {
@@ -206,21 +218,21 @@ __device__ __forceinline__ void run_taps(const typename Elem<MODE>::type* __rest
 }
 
 // ABF weight of one tap from its three shifted differences (src/adaptive_bilateral_filter_impl.cu:67-73, 103-105)
-template <bool CLAMP>
+template <int LK>
 __device__ __forceinline__ float abf_weight(const float d0, const float d1, const float d2, const float ks,
                                             const std::uint32_t lut_addr, const float clamp_f) {
     float dist = __fadd_rn(__fadd_rn(fabsf(d0), fabsf(d1)), fabsf(d2));
-    if constexpr (CLAMP) dist = fminf(dist, clamp_f);
+    if constexpr (lut_clamped(LK)) dist = fminf(dist, clamp_f);
     // (int)dist: bits(dist +rz 2^23) = 0x4b000000 + floor(dist); << 7 leaves 0x80000000 + 128*floor(dist),
-    // and lut_addr already carries the -0x80000000 (32-bit wrap-around)
-    const std::uint32_t addr = lut_addr + (__float_as_uint(__fadd_rz(dist, 8388608.f)) << 7);
+    // and lut_addr already carries the -0x80000000 (32-bit wrap-around; abf_index_bias for the other entry sizes)
+    const std::uint32_t addr = lut_addr + (__float_as_uint(__fadd_rz(dist, 8388608.f)) << lut_shift(LK));
     return __fmul_rn(ks, lds_f32(addr));
 }
 
 // ABF run: outputs are handled in pairs (2p, 2p+1).  Neighbour n is tap j = n - 2p of the first and tap j - 1 of
 // the second output; when both are inside the run the differences and the four accumulations are packed fp32x2
 // operations (same IEEE roundings per half as the scalar ones), otherwise the one valid output goes scalar.
-template <int P, int L, bool CLAMP>
+template <int P, int L, int LK>
 __device__ __forceinline__ void run_taps_abf(const std::uint32_t* __restrict__ t, const float* __restrict__ wp,
                                              const std::uint32_t lut_addr, const float clamp_f, Acc<kABF, P>& A) {
     float w[(L + 3) & ~3];
@@ -251,8 +263,8 @@ __device__ __forceinline__ void run_taps_abf(const std::uint32_t* __restrict__ t
                 unpack2(d0, d0l, d0h);
                 unpack2(d1, d1l, d1h);
                 unpack2(d2, d2l, d2h);
-                const float wl = abf_weight<CLAMP>(d0l, d1l, d2l, w[j], lut_addr, clamp_f);
-                const float wh = abf_weight<CLAMP>(d0h, d1h, d2h, w[j - 1], lut_addr, clamp_f);
+                const float wl = abf_weight<LK>(d0l, d1l, d2l, w[j], lut_addr, clamp_f);
+                const float wh = abf_weight<LK>(d0h, d1h, d2h, w[j - 1], lut_addr, clamp_f);
                 const unsigned long long ww = pack2(wl, wh);
                 fma2(A.s[0][p], ww, pack2(f0, f0));
                 fma2(A.s[1][p], ww, pack2(f1, f1));
@@ -279,7 +291,7 @@ __device__ __forceinline__ void run_taps_abf(const std::uint32_t* __restrict__ t
                 const float d0 = __fadd_rn(__fadd_rn(f0, nf[0]), no[0]);
                 const float d1 = __fadd_rn(__fadd_rn(f1, nf[1]), no[1]);
                 const float d2 = __fadd_rn(__fadd_rn(f2, nf[2]), no[2]);
-                const float wt = abf_weight<CLAMP>(d0, d1, d2, w[jj], lut_addr, clamp_f);
+                const float wt = abf_weight<LK>(d0, d1, d2, w[jj], lut_addr, clamp_f);
                 a[0] = __fmaf_rn(f0, wt, a[0]);
                 a[1] = __fmaf_rn(f1, wt, a[1]);
                 a[2] = __fmaf_rn(f2, wt, a[2]);
@@ -292,16 +304,16 @@ __device__ __forceinline__ void run_taps_abf(const std::uint32_t* __restrict__ t
 }
 
 // One window row of len = 2*hw+1 taps: runs of 8, then the odd remainder.
-template <int MODE, int P, bool CLAMP>
+template <int MODE, int P, int LK>
 __device__ __forceinline__ void do_row(int len, const typename Elem<MODE>::type* __restrict__ t,
                                        const float* __restrict__ wp, const std::uint32_t lut_addr,
                                        const std::uint32_t clamp_i, const float clamp_f, Acc<MODE, P>& A) {
     auto run = [&](auto lc) {
         constexpr int L = decltype(lc)::value;
         if constexpr (MODE == kABF) {
-            run_taps_abf<P, L, CLAMP>(t, wp, lut_addr, clamp_f, A);
+            run_taps_abf<P, L, LK>(t, wp, lut_addr, clamp_f, A);
         } else {
-            run_taps<MODE, P, L, CLAMP>(t, wp, lut_addr, clamp_i, clamp_f, A);
+            run_taps<MODE, P, L, LK>(t, wp, lut_addr, clamp_i, clamp_f, A);
         }
     };
 #pragma unroll 1
@@ -320,7 +332,7 @@ struct SmemLayout {
     int tile_pitch, tile_w, tile_h, hs_pitch, w_pitch, group_stride;
 };
 
-__host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, int lut_n, int n_groups) {
+__host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, int lut_n, int lut_kind, int n_groups) {
     SmemLayout L;
     const int k = 2 * radius + 1;
     L.tile_w = kWarps * P + 2 * radius;
@@ -329,7 +341,7 @@ __host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, i
     L.hs_pitch = (kWarps * P) | 1;
     int off = 0;
     L.lut_off = off;
-    off += lut_n * 32 * 4;
+    off += lut_n << lut_shift(lut_kind);
     L.w_pitch = (k + 7) & ~7;  // row ky: its 2*hw+1 non-zero weights from index 0, zero padded
     L.w_off = off;
     off += k * L.w_pitch * 4;
@@ -352,7 +364,7 @@ __host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, i
     return L;
 }
 
-template <int MODE, int P, bool CLAMP>
+template <int MODE, int P, int LK>
 __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
     stencil_kernel(const StencilArgs a, const int tiles_x, const int n_tiles) {
     using E = typename Elem<MODE>::type;
@@ -361,7 +373,7 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
     const int k = 2 * radius + 1;
     const int n_groups = blockDim.x / kThreads;
     const int group = threadIdx.x / kThreads;  // warp group: its own tile buffer, named barrier and tile sequence
-    const SmemLayout L = make_layout(MODE, P, radius, a.lut_n, n_groups);
+    const SmemLayout L = make_layout(MODE, P, radius, a.lut_n, LK, n_groups);
     float* const lut_s = reinterpret_cast<float*>(smem + L.lut_off);
     float* const w_s = reinterpret_cast<float*>(smem + L.w_off);
     int* const hw_s = reinterpret_cast<int*>(smem + L.hw_off);
@@ -376,7 +388,8 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
     auto group_sync = [&]() { asm volatile("bar.sync %0, %1;" ::"r"(group + 1), "n"(kThreads) : "memory"); };
 
     // one-time per CTA (shared by all groups): replicated LUT, spatial weight rows, half widths
-    for (int i = threadIdx.x; i < a.lut_n * 32; i += blockDim.x) lut_s[i] = __ldg(a.lut + (i >> 5));
+    constexpr int kRepLog2 = lut_shift(LK) - 2;  // copies per entry (log2)
+    for (int i = threadIdx.x; i < (a.lut_n << kRepLog2); i += blockDim.x) lut_s[i] = __ldg(a.lut + (i >> kRepLog2));
     for (int i = threadIdx.x; i < k * L.w_pitch; i += blockDim.x) {
         const int row = i / L.w_pitch, j = i - row * L.w_pitch;
         const int hw = __ldg(a.hw + row);
@@ -387,8 +400,9 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
     __syncthreads();
 
     // byte address of this lane's copy of entry 0; ABF folds the 2^23 bias of its index trick in (see run_taps)
-    const std::uint32_t lut_addr = static_cast<std::uint32_t>(__cvta_generic_to_shared(lut_s + lane)) -
-                                   (MODE == kABF ? 0x80000000u : 0u);
+    const std::uint32_t lut_addr =
+        static_cast<std::uint32_t>(__cvta_generic_to_shared(lut_s + (lane & ((1 << kRepLog2) - 1)))) -
+        (MODE == kABF ? abf_index_bias(LK) : 0u);
     const std::uint32_t clamp_i = static_cast<std::uint32_t>(a.lut_n - 1);
     const float clamp_f = static_cast<float>(a.lut_n - 1);
     const int W = a.width, H = a.height;
@@ -549,7 +563,7 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
 #pragma unroll 1
         for (int ky = -radius; ky <= radius; ++ky) {
             const int hw = hw_s[ky + radius];
-            do_row<MODE, P, CLAMP>(2 * hw + 1, tcentre + ky * tp - hw, w_s + (ky + radius) * L.w_pitch, lut_addr, clamp_i,
+            do_row<MODE, P, LK>(2 * hw + 1, tcentre + ky * tp - hw, w_s + (ky + radius) * L.w_pitch, lut_addr, clamp_i,
                                    clamp_f, A);
         }
 
@@ -665,20 +679,20 @@ __global__ void stencil_generic_kernel(const StencilArgs a, const int lut_len) {
 // 80 registers that 24 warps per SM allow
 constexpr int outputs_per_thread(int mode) { return mode == kABF ? 4 : 8; }
 
-// Warp groups per CTA that fit the shared-memory budget with `lut_n` replicated entries (0: none).
-int groups_that_fit(int mode, int radius, int lut_n) {
+// Warp groups per CTA that fit the shared-memory budget with `lut_n` table entries of kind `lut_kind` (0: none).
+int groups_that_fit(int mode, int radius, int lut_n, int lut_kind) {
     for (int g = kMaxGroups; g >= 1; --g)
-        if (make_layout(mode, outputs_per_thread(mode), radius, lut_n, g).total <= kSmemBudget) return g;
+        if (make_layout(mode, outputs_per_thread(mode), radius, lut_n, lut_kind, g).total <= kSmemBudget) return g;
     return 0;
 }
 
-template <int MODE, bool CLAMP>
+template <int MODE, int LK>
 cudaError_t launch_tiled(const StencilArgs& a, int sm_count, cudaStream_t stream) {
     constexpr int P = outputs_per_thread(MODE);
-    const int n_groups = groups_that_fit(MODE, a.radius, a.lut_n);
-    if (n_groups < 1) return cudaErrorInvalidConfiguration;
-    const SmemLayout L = make_layout(MODE, P, a.radius, a.lut_n, n_groups);
-    auto kern = stencil_kernel<MODE, P, CLAMP>;
+    const int n_groups = groups_that_fit(MODE, a.radius, a.lut_n, LK);
+    if (n_groups < 1) return cudaErrorInvalidConfiguration;  // stencil_pick_lut never hands out such a table
+    const SmemLayout L = make_layout(MODE, P, a.radius, a.lut_n, LK, n_groups);
+    auto kern = stencil_kernel<MODE, P, LK>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total);
     if (e != cudaSuccess) return e;
     const int tiles_x = (a.width + kWarps * P - 1) / (kWarps * P);
@@ -690,6 +704,15 @@ cudaError_t launch_tiled(const StencilArgs& a, int sm_count, cudaStream_t stream
     kern<<<grid, kThreads * n_groups, L.total, stream>>>(a, tiles_x, n_tiles);
     count_launch();
     return cudaGetLastError();
+}
+
+template <int MODE>
+cudaError_t launch_tiled_kind(const StencilArgs& a, int sm_count, cudaStream_t stream) {
+    switch (a.lut_kind) {
+        case kLutFull: return launch_tiled<MODE, kLutFull>(a, sm_count, stream);
+        case kLutClamp: return launch_tiled<MODE, kLutClamp>(a, sm_count, stream);
+        default: return launch_tiled<MODE, kLutNarrow>(a, sm_count, stream);
+    }
 }
 
 template <int MODE>
@@ -705,18 +728,29 @@ cudaError_t launch_generic(const StencilArgs& a, cudaStream_t stream) {
 
 int stencil_max_tiled_radius() { return kMaxTiledRadius; }
 
-void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, int* lut_n, int* clamp) {
-    // The whole table, replicated 32x, is shared by the warp groups of the one CTA an SM runs: when it fits next to
-    // kMaxGroups tile buffers no index clamp is needed.  Otherwise trailing zeros are cut: every index > last_nz has
-    // weight exactly 0, so clamping the index to last_nz+1 (a zero entry) is bit-neutral.
+void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, int* lut_n, int* lut_kind) {
+    // The table is shared by the warp groups of the one CTA an SM runs.  Candidates, in order of preference at an equal
+    // number of warp groups: the whole table 32x replicated (no clamp instruction); the table cut after its last
+    // non-zero entry -- every index > last_nz has weight exactly 0, so clamping the index to last_nz+1 (a zero entry)
+    // is bit-neutral; the cut table 8x replicated.  More resident warp groups win over a conflict-free table: a single
+    // 256-thread group per SM cannot hide the LDS / I2F latencies of the tap loop.
     *lut_n = table_len;
-    *clamp = 0;
+    *lut_kind = kLutFull;
     if (radius > kMaxTiledRadius) return;
-    const bool zero_tail = last_nz + 1 < table_len;
-    if (groups_that_fit(mode, radius, table_len) == kMaxGroups || !zero_tail) return;
-    if (groups_that_fit(mode, radius, last_nz + 2) <= groups_that_fit(mode, radius, table_len)) return;
-    *lut_n = last_nz + 2;
-    *clamp = 1;
+    const int cut_n = last_nz + 2 < table_len ? last_nz + 2 : table_len;
+    const int g_full = groups_that_fit(mode, radius, table_len, kLutFull);
+    const int g_cut = groups_that_fit(mode, radius, cut_n, kLutClamp);
+    const int g_narrow = groups_that_fit(mode, radius, cut_n, kLutNarrow);
+    int best = g_full;
+    if (g_cut > best) {
+        best = g_cut;
+        *lut_n = cut_n;
+        *lut_kind = kLutClamp;
+    }
+    if (g_narrow > best) {
+        *lut_n = cut_n;
+        *lut_kind = kLutNarrow;
+    }
 }
 
 cudaError_t launch_stencil(StencilMode mode, const StencilArgs& a, int sm_count, cudaStream_t stream) {
@@ -728,14 +762,10 @@ cudaError_t launch_stencil(StencilMode mode, const StencilArgs& a, int sm_count,
             default: return launch_generic<kABF>(a, stream);
         }
     }
-    const bool clamp = a.lut_clamp != 0;
     switch (mode) {
-        case kBF:
-            return clamp ? launch_tiled<kBF, true>(a, sm_count, stream) : launch_tiled<kBF, false>(a, sm_count, stream);
-        case kJBF:
-            return clamp ? launch_tiled<kJBF, true>(a, sm_count, stream) : launch_tiled<kJBF, false>(a, sm_count, stream);
-        default:
-            return clamp ? launch_tiled<kABF, true>(a, sm_count, stream) : launch_tiled<kABF, false>(a, sm_count, stream);
+        case kBF: return launch_tiled_kind<kBF>(a, sm_count, stream);
+        case kJBF: return launch_tiled_kind<kJBF>(a, sm_count, stream);
+        default: return launch_tiled_kind<kABF>(a, sm_count, stream);
     }
 }
 

@@ -25,7 +25,7 @@ struct StencilArgs {
     int radius;
     const float* lut;           // device: colour table (768 or 1536 floats)
     int lut_n;                  // entries replicated into shared memory
-    int lut_clamp;              // 1: index is clamped to lut_n-1 (whose entry, and all after it, is 0)
+    int lut_kind;               // LutKind of stencil.cu: replication of the table and whether the index is clamped to lut_n-1
     const int* hw;              // device: 2r+1 half widths, hw[ky+r] = floor(sqrt(r^2-ky^2))
     const float* ks_full;       // device: ksize*ksize spatial kernel (row ky: its 2*hw+1 non-zero weights are copied to shared memory)
 };
@@ -34,7 +34,7 @@ cudaError_t launch_stencil(StencilMode mode, const StencilArgs& a, int sm_count,
 // Largest radius the tiled kernels cover; beyond it the generic one-thread-per-pixel kernel runs.
 int stencil_max_tiled_radius();
 // Decides how many colour-table entries are replicated in shared memory and whether the index is clamped.
-void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, int* lut_n, int* clamp);
+void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, int* lut_n, int* lut_kind);
 
 // gradient.cu
 cudaError_t launch_gradient_u8(const std::uint8_t* src, float* dst, int width, int height, int channels, int src_y0,
