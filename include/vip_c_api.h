@@ -188,7 +188,8 @@ VIP_API int vip_integral_get(const void* d_table, int width, int height, int cha
  *   ctor/execute -> Impl::Impl / Impl::execute                src/bilateral_texture_filter_impl.cu:179-214
  *   vip_btf_blur_rtv -> Impl::compute_blur_and_rtv + kernel   src/bilateral_texture_filter_impl.cu:10-104, 216-237
  *   vip_btf_guide    -> Impl::compute_guide + kernel          src/bilateral_texture_filter_impl.cu:106-177, 239-256
- * The joint bilateral step uses (ksize 2k-1, sigma_space k-1, sigma_color sqrt(3)) like the reference (:188).
+ * The joint bilateral step uses (ksize 2k-1, sigma_space k-1, sigma_color sqrt(3)) like the reference (:188);
+ * ksize 1 would make sigma_space 0 (the reference divides by zero building its table): VIP_E_KSIZE, ksize >= 3.
  * The object owns its scratch buffers; a run is not re-entrant on the same object (same as the reference). */
 typedef struct vip_btf vip_btf;
 VIP_API int vip_btf_create(vip_btf** out, int width, int height, int ksize, int nitr);

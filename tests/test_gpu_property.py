@@ -11,7 +11,7 @@ hyp = pytest.importorskip("hypothesis")
 from hypothesis import HealthCheck, given, settings, strategies as st  # noqa: E402
 
 pytestmark = pytest.mark.gpu
-SET = dict(max_examples=25, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow])
+SET = dict(max_examples=60, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow])
 
 
 @pytest.fixture(scope="module")
@@ -70,7 +70,7 @@ def test_abf_random_cases(vip, wh, k, ss, sc, kind, seed):
 
 
 @settings(max_examples=12, deadline=None, suppress_health_check=SET["suppress_health_check"])
-@given(wh=st.tuples(st.integers(20, 120), st.integers(40, 90)), k=st.sampled_from([3, 5, 9]), nitr=st.integers(1, 3),
+@given(wh=st.tuples(st.integers(1, 120), st.integers(1, 90)), k=st.sampled_from([3, 5, 9, 13]), nitr=st.integers(0, 3),
        kind=st.sampled_from(["rand", "narrow", "smooth"]), seed=st.integers(0, 10**6))
 def test_btf_stages_random_cases(vip, wh, k, nitr, kind, seed):
     """blur / mRTV and guide stages exact (integer + ordered-float arithmetic); the end-to-end filter equals the oracle
@@ -118,3 +118,53 @@ def test_two_strips_equal_whole_image(vip, w, h, k, cut, kind, seed):
         torch.cuda.synchronize()
         out[y0:y1] = d.cpu().numpy()
     assert np.array_equal(out, whole.cpu().numpy())
+
+
+# ------------------------------------------------------------------ streaming stages (numpy restatements are exact)
+@settings(**SET)
+@given(wh=st.tuples(st.integers(1, 700), st.integers(1, 60)), ch=st.integers(1, 4), f32=st.booleans(), seed=st.integers(0, 10**6))
+def test_gradient_random_cases(vip, wh, ch, f32, seed):
+    w, h = wh
+    rs = np.random.RandomState(seed)
+    src = rs.randint(0, 256, size=(h, w, ch)).astype(np.uint8)
+    if f32:
+        src = (src.astype(np.float32) * np.float32(1.37)).astype(np.float32)
+    d = torch.empty((h, w), dtype=torch.float32, device="cuda")
+    vip.cuda_gradient(dev(src), d, w, h, ch)
+    torch.cuda.synchronize()
+    assert np.array_equal(d.cpu().numpy(), O.o_gradient(src if ch > 1 else src[..., 0]))
+
+
+@settings(**SET)
+@given(wh=st.tuples(st.integers(1, 900), st.integers(1, 300)), r=st.integers(0, 20), ch=st.integers(1, 4),
+       dtype=st.sampled_from([np.uint8, np.uint16]), seed=st.integers(0, 10**6))
+def test_integral_table_random_cases(vip, wh, r, ch, dtype, seed):
+    """Border-replicated integral table of any size / radius / channel count, exact modulo 2^32 (the integer tables of
+    the reference are int, include/cpp/border_replicated_integral_image.hpp)."""
+    w, h = wh
+    src = np.random.RandomState(seed).randint(0, np.iinfo(dtype).max + 1, size=(h, w, ch)).astype(dtype)
+    ii = vip.CudaBorderReplicatedIntegralImage(w, h, r, ch, dtype)
+    ii.build(dev(src))
+    torch.cuda.synchronize()
+    got = ii.download_table().reshape(h + 2 * r + 1, w + 2 * r + 1, ch)
+    pad = np.pad(src.astype(np.uint64), ((r, r), (r, r), (0, 0)), mode="edge")
+    want = np.pad(np.cumsum(np.cumsum(pad, 0), 1), ((1, 0), (1, 0), (0, 0)))
+    assert np.array_equal(got, (want & 0xFFFFFFFF).astype(np.uint32))
+
+
+@settings(**SET)
+@given(wh=st.tuples(st.integers(1, 500), st.integers(1, 40)), ch=st.sampled_from([1, 3, 4]), swap=st.booleans(),
+       so=st.integers(0, 3), do=st.integers(0, 3), seed=st.integers(0, 10**6))
+def test_convert_random_cases(vip, wh, ch, swap, so, do, seed):
+    """convert_to_3ch on the device (sample/benchmark/main.cpp:91-103) at any size and any byte alignment of either buffer."""
+    w, h = wh
+    src = np.random.RandomState(seed).randint(0, 256, size=(h, w, ch)).astype(np.uint8)
+    sbuf = torch.zeros((h * w * ch + so,), dtype=torch.uint8, device="cuda")
+    sbuf[so:] = dev(src).reshape(-1)
+    dbuf = torch.full((h * w * 3 + do + 8,), 77, dtype=torch.uint8, device="cuda")
+    vip.convert_to_bgr(sbuf[so:], ch, dbuf[do:], w, h, swap)
+    torch.cuda.synchronize()
+    want = np.repeat(src, 3, axis=2) if ch == 1 else (src[..., 2::-1] if swap else src[..., :3])
+    out = dbuf.cpu().numpy()
+    assert np.array_equal(out[do:do + h * w * 3].reshape(h, w, 3), want)
+    assert np.all(out[:do] == 77) and np.all(out[do + h * w * 3:] == 77)          # nothing written outside the image
