@@ -359,11 +359,13 @@ def main():
         alg_bytes = local_pixels * 9.0                    # dominant kernel = joint bilateral: src + guide in, dst out
         kernel_ms = None                                  # several kernels per step: see profiles/ for the split
         instr_per_tap = 8.5                               # JBF 17x17: smsp__inst_executed x 32 / taps (ncu, profiles/r01d)
+        packed_per_tap = 2.0
         taps_per_px = taps * nitr + (2 * mask_taps(radius) if filt == "all" else 0)
     else:
         alg_bytes = local_pixels * 6.0                    # 3 B in + 3 B out per pixel
         kernel_ms = ms_step
         instr_per_tap = 18.1 if filt == "abf" else 7.8   # whole-kernel SASS instructions per tap measured by ncu (profiles/r01d; tile staging, box sums and epilogue included)
+        packed_per_tap = 4.2 if filt == "abf" else 2.0   # fp32x2 instructions among them (SASS of the tap loop): ABF 6 FADD2 + 4 FFMA2 per tap PAIR less the scalar edge taps; BF/JBF 1 FFMA2 {s0,s1} + 2 per pair {s2},{sk}
         taps_per_px = taps
     traffic = None
     try:
@@ -387,6 +389,24 @@ def main():
              "est_issue_util": taps_s * instr_per_tap / issue_peak, "sm_mhz_used": sm_mhz,
              "peak_thread_instr_per_s": issue_peak,
              "note": "taps/s x SASS instructions per tap (ncu smsp__inst_executed of the same kernel, profiles/) / (SMs x 4 x 32 x clock); packed fp32x2 instructions count once here but hold the dispatch port twice, see DESIGN.md 3"}
+    # measured issue roofs (SURVEY.md 8d asks for an FFMA micro-kernel on the box): tools/probe/issue_probe.cu, a few ms each
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import peaks as _peaks
+        _pl = _peaks.load()
+        if _pl is not None and rank == 0:
+            ffma, _ = _peaks.measure(_pl, 0)
+            ffma2, _ = _peaks.measure(_pl, 1)
+            issue["measured_ffma_thread_instr_per_s"] = ffma
+            issue["measured_ffma2_packed_instr_per_s"] = ffma2
+            # a packed fp32x2 instruction holds the dispatch port for two slots (measured: the FFMA2 rate is half the FFMA
+            # rate), so the slots a tap costs are instr + packed; their rate against the measured FFMA rate is the fraction of
+            # the stencil's own roofline -- the number to read instead of roofline.frac for these kernels
+            issue["packed_instr_per_tap"] = packed_per_tap
+            issue["dispatch_slots_per_tap"] = instr_per_tap + packed_per_tap
+            issue["frac_of_measured_issue_roof"] = taps_s * (instr_per_tap + packed_per_tap) / ffma
+    except Exception as exc:                                 # the probe is optional evidence, never a reason to fail the bench
+        issue["probe_error"] = str(exc)
 
     cpu = None
     if not args.no_cpu_baseline:

@@ -44,8 +44,14 @@ def main():
         w, h = map(int, size.split("x"))
         k = int(k)
         rs = np.random.RandomState(42)
-        if content == "rand":
+        if content == "rand":                                     # S-rand, the headline content
             img = rs.randint(0, 256, size=(h, w, 3)).astype(np.uint8)
+        elif content == "narrow":                                 # S-narrow: the reference benchmark's uniform [100, 120)
+            img = rs.randint(100, 120, size=(h, w, 3)).astype(np.uint8)
+        elif content == "lenna":                                  # S-nat: the reference's sample image, mirrored tiling
+            t = np.load(os.path.join(ROOT, "tests", "golden", "lenna_vectors.npz"))["lenna_bgr"]
+            t = np.concatenate([np.concatenate([t, t[:, ::-1]], 1), np.concatenate([t[::-1], t[::-1, ::-1]], 1)], 0)
+            img = np.ascontiguousarray(np.tile(t, (h // t.shape[0] + 1, w // t.shape[1] + 1, 1))[:h, :w])
         else:
             t = O.smooth_image(256, 216, seed=8)
             img = np.ascontiguousarray(np.tile(t, (h // 216 + 1, w // 256 + 1, 1))[:h, :w])
