@@ -218,6 +218,15 @@ VIP_API size_t vip_btf_scratch_bytes(const vip_btf* f);
 typedef struct vip_mg vip_mg;
 VIP_API int vip_mg_create(vip_mg** out, const int* device_ids, int n_devices, int kind, int width, int height,
                           int ksize, float sigma_space, float sigma_color, int nitr);
+/* Same with flags.  BTF strips get the 17 (k = 9) rows of the previous iterate every iteration needs either from
+ * buffers that carry nitr x 17 halo rows from the scatter, recomputing the shrinking overlap redundantly (no
+ * communication, VIP_MG_FLAG_BTF_DEEP_HALO), or by a peer-to-peer halo exchange after every iteration
+ * (VIP_MG_FLAG_BTF_EXCHANGE).  0 = automatic: deep halo while the redundant rows are <= 35 % of a strip.  The
+ * results are bit-identical either way. */
+#define VIP_MG_FLAG_BTF_EXCHANGE 1
+#define VIP_MG_FLAG_BTF_DEEP_HALO 2
+VIP_API int vip_mg_create_ex(vip_mg** out, const int* device_ids, int n_devices, int kind, int width, int height,
+                             int ksize, float sigma_space, float sigma_color, int nitr, int flags);
 VIP_API int vip_mg_destroy(vip_mg* m);
 /* Row range [*y0, *y0 + *rows) owned by device slot `i`. */
 VIP_API int vip_mg_strip_rows(const vip_mg* m, int i, int* y0, int* rows);

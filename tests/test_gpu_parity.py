@@ -500,6 +500,18 @@ def test_multigpu_driver_virtual_devices(vip, kind, k, n):
     assert mg.last_run_ms() > 0
 
 
+@pytest.mark.parametrize("mode", ["deep", "exchange", "auto"])
+@pytest.mark.parametrize("n,h,nitr,k", [(2, 140, 3, 9), (3, 200, 2, 9), (4, 120, 3, 5), (2, 60, 4, 9), (2, 700, 3, 9)])
+def test_multigpu_btf_halo_modes(vip, mode, n, h, nitr, k):
+    """BTF strips: nitr x 17 halo rows with redundant recompute ('deep') and the per-iteration peer-to-peer refresh
+    ('exchange') give the single-GPU result bit for bit; 'auto' is one of the two."""
+    w = 96
+    img = O.smooth_image(w, h, seed=n + h)
+    mg = vip.MultiGpuFilter([i % torch.cuda.device_count() for i in range(n)], "btf", w, h, ksize=k, nitr=nitr, btf_halo=mode)
+    assert np.array_equal(mg.execute(img), run_btf(vip, img, k, nitr))
+    assert np.array_equal(mg.execute(img), run_btf(vip, img, k, nitr))       # a second run on the same object
+
+
 def test_multigpu_driver_many_slots_create_destroy(vip):
     """8 slots (the 8 x B200 box) on whatever devices exist: the worker threads start / stop cleanly, repeatedly."""
     n = torch.cuda.device_count()

@@ -28,12 +28,18 @@ def main():
     devs = list(range(args.gpus))
     rs = np.random.RandomState(42)
 
-    for name, kind, w, h, k, nitr in (("bf_8k_r15_strips", "bf", 7680, 4320, 31, 0), ("abf_4k_r7_strips", "abf", 3840, 2160, 15, 0),
-                                      ("btf_4k_strips", "btf", 3840, 2160, 9, 3)):
+    ap_only = os.environ.get("MG_ONLY", "")
+    for name, kind, w, h, k, nitr, mode in (("bf_8k_r15_strips", "bf", 7680, 4320, 31, 0, None), ("abf_4k_r7_strips", "abf", 3840, 2160, 15, 0, None),
+                                            ("btf_4k_strips_deep_halo", "btf", 3840, 2160, 9, 3, "deep"),
+                                            ("btf_4k_strips_exchange", "btf", 3840, 2160, 9, 3, "exchange"),
+                                            ("btf_8k_strips_deep_halo", "btf", 7680, 4320, 9, 3, "deep"),
+                                            ("btf_8k_strips_exchange", "btf", 7680, 4320, 9, 3, "exchange")):
+        if ap_only and not name.startswith(ap_only):
+            continue
         img = rs.randint(0, 256, size=(h, w, 3)).astype(np.uint8)
         hin, hout = vip.PinnedBuffer(img.size), vip.PinnedBuffer(img.size)
         hin.array[:] = img.reshape(-1)
-        mg = vip.MultiGpuFilter(devs, kind, w, h, ksize=k, nitr=nitr)
+        mg = vip.MultiGpuFilter(devs, kind, w, h, ksize=k, nitr=nitr, btf_halo=mode)
         src, dst = hin.array.reshape(h, w, 3), hout.array.reshape(h, w, 3)
         mg.scatter_host(src)
         mg.run()
@@ -53,6 +59,8 @@ def main():
                           "e2e_mpixel_per_s": w * h / np.median(e2e_ms) / 1e3}), flush=True)
         del mg
 
+    if ap_only:
+        return
     w, h, nf = 1920, 1080, args.frames
     frames = vip.PinnedBuffer(nf * w * h * 3)
     out = vip.PinnedBuffer(nf * w * h * 3)

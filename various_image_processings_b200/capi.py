@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("VIP_B200_LIB") or os.path.join(_HERE, "lib", "libvip_
 VIP_OK = 0
 VIP_LUT_CUDA, VIP_LUT_CPU = 0, 1
 VIP_MG_BF, VIP_MG_ABF, VIP_MG_BTF = 0, 1, 2
+VIP_MG_FLAG_BTF_EXCHANGE, VIP_MG_FLAG_BTF_DEEP_HALO = 1, 2
 VIP_SRC_U8, VIP_SRC_U16, VIP_SRC_F32 = 0, 1, 2
 
 
@@ -84,6 +85,7 @@ SIGNATURES = {
     "vip_btf_iterate_strip": (_i, [_vp, _vp, _vp, C.POINTER(Strip), _vp]),
     "vip_btf_scratch_bytes": (_sz, [_vp]),
     "vip_mg_create": (_i, [_pp, C.POINTER(C.c_int), _i, _i, _i, _i, _i, _f, _f, _i]),
+    "vip_mg_create_ex": (_i, [_pp, C.POINTER(C.c_int), _i, _i, _i, _i, _i, _f, _f, _i, _i]),
     "vip_mg_destroy": (_i, [_vp]),
     "vip_mg_strip_rows": (_i, [_vp, _i, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "vip_mg_scatter_host": (_i, [_vp, _vp]),

@@ -3,10 +3,16 @@
 //   * a large image is cut into contiguous row strips, one per device slot; every strip buffer carries `halo`
 //     rows of its neighbours on each side; kernels clamp against the FULL image, so the strip results are
 //     bit-identical to a single-GPU run;
-//   * BF / ABF need their halo once (it comes with the scatter); BTF refreshes 17 halo rows (k = 9) of the new
-//     iterate after every iteration: the receiving device's stream waits for the neighbour's "iteration done"
-//     event and then pulls the rows with cudaMemcpyPeerAsync (NVLink P2P when peer access is enabled), so the
-//     exchange is ordered by events only -- no host synchronisation inside the iteration loop;
+//   * BF / ABF need their halo once (it comes with the scatter).  BTF needs 17 rows (k = 9) of the previous
+//     iterate per iteration and has two ways to get them:
+//       deep halo  the strip buffers carry nitr x 17 rows per side from the scatter; iteration `it` recomputes the
+//                  shrinking overlap (nitr-1-it) x 17 rows per side redundantly -- no communication and no
+//                  cross-device ordering at all (12.6 % extra rows at 4K on 8 devices);
+//       exchange   17 halo rows of the new iterate are refreshed after every iteration: the receiving device's
+//                  stream waits for the neighbour's "iteration done" event and pulls the rows with
+//                  cudaMemcpyPeerAsync (NVLink P2P when peer access is enabled) -- events only, no host
+//                  synchronisation inside the iteration loop;
+//     vip_mg_create picks deep halo while the redundant rows stay under 35 % of a strip (VIP_MG_FLAG_* overrides);
 //   * every device slot has its own host worker thread that enqueues the slot's work (kernels, event records, peer
 //     copies): with one enqueueing thread the 8 x 3 x (3 launches + events + 2 peer copies) calls of a BTF run cost
 //     more host time than the GPUs need for the work.  Workers only order themselves through one atomic counter per
@@ -71,6 +77,7 @@ struct vip_mg {
     int n = 0, kind = 0, width = 0, height = 0, ksize = 0, nitr = 0, halo = 0;
     float ss = 0.f, sc = 0.f;
     int result_buf = 0;  // BTF: which of buf[0/1] holds the final iterate (-1: src)
+    bool btf_deep = false;  // BTF: deep-halo mode (no exchange), see the header comment
     bool batch_ready = false;
     std::vector<Slot> slots;
     std::vector<std::unique_ptr<Worker>> workers;          // one enqueueing thread per slot
@@ -132,9 +139,13 @@ int enqueue_slot(vip_mg* m, int i) {
         for (int it = 0; it < m->nitr; it++) {
             const int ob = it & 1;
             const uint8_t* in = (it == 0) ? s.src : s.buf[ob ^ 1];
-            const vip_strip st{s.sy0, s.srows, s.sy0, s.y0, s.rows};
+            // deep halo: this iterate must also cover what the remaining iterations will read around the owned rows
+            const int margin = m->btf_deep ? (m->nitr - 1 - it) * m->halo : 0;
+            const int oy0 = std::max(0, s.y0 - margin), oy1 = std::min(m->height, s.y0 + s.rows + margin);
+            const vip_strip st{s.sy0, s.srows, s.sy0, oy0, oy1 - oy0};
             const int rc = vip_btf_iterate_strip(s.btf, in, s.buf[ob], &st, s.stream);
             if (rc != VIP_OK) return rc;
+            if (m->btf_deep) continue;
             if ((e = cudaEventRecord(s.ev_iter[it], s.stream)) != cudaSuccess) return cu(e);
             m->iter_recorded[i].store(it + 1, std::memory_order_release);
             if (it + 1 < m->nitr) {
@@ -215,6 +226,11 @@ extern "C" {
 
 int vip_mg_create(vip_mg** out, const int* device_ids, int n_devices, int kind, int width, int height, int ksize,
                   float sigma_space, float sigma_color, int nitr) {
+    return vip_mg_create_ex(out, device_ids, n_devices, kind, width, height, ksize, sigma_space, sigma_color, nitr, 0);
+}
+
+int vip_mg_create_ex(vip_mg** out, const int* device_ids, int n_devices, int kind, int width, int height, int ksize,
+                     float sigma_space, float sigma_color, int nitr, int flags) {
     if (!out || !device_ids) return VIP_E_NULL;
     *out = nullptr;
     if (n_devices < 1 || n_devices > 64) return VIP_E_DEVICE;
@@ -227,8 +243,16 @@ int vip_mg_create(vip_mg** out, const int* device_ids, int n_devices, int kind, 
     for (int i = 0; i < n_devices; i++)
         if (device_ids[i] < 0 || device_ids[i] >= ndev) return VIP_E_DEVICE;
     const int halo = (kind == VIP_MG_BTF) ? (ksize - 1) + 2 * (ksize / 2) + 1 : ksize / 2;
-    // every strip must be able to serve a neighbour's halo from its own rows
-    if (n_devices > 1 && height / n_devices < halo) return VIP_E_SIZE;
+    if ((flags & VIP_MG_FLAG_BTF_EXCHANGE) && (flags & VIP_MG_FLAG_BTF_DEEP_HALO)) return VIP_E_UNSUPPORTED;
+    bool deep = false;
+    if (kind == VIP_MG_BTF && n_devices > 1 && nitr > 1) {
+        // redundant rows of the deep-halo mode, averaged over the iterations: (nitr-1) x halo per strip
+        const long long extra = static_cast<long long>(nitr - 1) * halo, strip = height / n_devices;
+        deep = (flags & VIP_MG_FLAG_BTF_DEEP_HALO) || (!(flags & VIP_MG_FLAG_BTF_EXCHANGE) && extra * 100 <= strip * 35);
+    }
+    // exchange mode: every strip must be able to serve a neighbour's halo from its own rows
+    if (n_devices > 1 && !deep && height / n_devices < halo) return VIP_E_SIZE;
+    const int buf_halo = deep ? nitr * halo : halo;   // rows the strip buffers carry on each side
 
     DeviceGuard guard;
     vip_mg* m = new (std::nothrow) vip_mg();
@@ -240,6 +264,7 @@ int vip_mg_create(vip_mg** out, const int* device_ids, int n_devices, int kind, 
     m->ksize = ksize;
     m->nitr = nitr;
     m->halo = halo;
+    m->btf_deep = deep;
     m->ss = sigma_space;
     m->sc = sigma_color;
     m->slots.resize(n_devices);
@@ -250,8 +275,8 @@ int vip_mg_create(vip_mg** out, const int* device_ids, int n_devices, int kind, 
         s.device = device_ids[i];
         s.y0 = static_cast<int>(static_cast<long long>(height) * i / n_devices);
         s.rows = static_cast<int>(static_cast<long long>(height) * (i + 1) / n_devices) - s.y0;
-        s.sy0 = std::max(0, s.y0 - halo);
-        s.srows = std::min(height, s.y0 + s.rows + halo) - s.sy0;
+        s.sy0 = std::max(0, s.y0 - buf_halo);
+        s.srows = std::min(height, s.y0 + s.rows + buf_halo) - s.sy0;
         if ((e = cudaSetDevice(s.device)) != cudaSuccess) { rc = cu(e); break; }
         // P2P with the neighbouring slots (an error only means "already enabled" or "not supported":
         // cudaMemcpyPeerAsync then falls back to staging through the host)

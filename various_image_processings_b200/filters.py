@@ -316,12 +316,17 @@ class MultiGpuFilter:
     (vip_mg_* in include/vip_c_api.h).  kind: 'bf' | 'abf' | 'btf'."""
     KINDS = {"bf": capi.VIP_MG_BF, "abf": capi.VIP_MG_ABF, "btf": capi.VIP_MG_BTF}
 
-    def __init__(self, device_ids, kind, width, height, ksize=9, sigma_space=10.0, sigma_color=30.0, nitr=3):
+    BTF_HALO = {None: 0, "auto": 0, "exchange": capi.VIP_MG_FLAG_BTF_EXCHANGE, "deep": capi.VIP_MG_FLAG_BTF_DEEP_HALO}
+
+    def __init__(self, device_ids, kind, width, height, ksize=9, sigma_space=10.0, sigma_color=30.0, nitr=3,
+                 btf_halo=None):
+        """btf_halo: 'deep' (nitr x 17 halo rows, redundant recompute, no communication), 'exchange' (17 rows refreshed
+        peer-to-peer after every iteration) or None / 'auto' (vip_mg_create_ex decides)."""
         self.width, self.height, self.n = width, height, len(device_ids)
         ids = (C.c_int * len(device_ids))(*device_ids)
         self._h = C.c_void_p()
-        check(lib().vip_mg_create(C.byref(self._h), ids, len(device_ids), self.KINDS[kind], width, height, ksize,
-                                  sigma_space, sigma_color, nitr), "vip_mg_create")
+        check(lib().vip_mg_create_ex(C.byref(self._h), ids, len(device_ids), self.KINDS[kind], width, height, ksize,
+                                     sigma_space, sigma_color, nitr, self.BTF_HALO[btf_halo]), "vip_mg_create_ex")
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
