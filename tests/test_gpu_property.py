@@ -94,12 +94,12 @@ def test_btf_stages_random_cases(vip, wh, k, nitr, kind, seed):
     torch.cuda.synchronize()
     og = O.o_guide(obl, ort, k)
     dg = np.abs(g.cpu().numpy().astype(int) - og.astype(int))
-    assert dg.max() <= 1 and (dg != 0).mean() < 1e-3            # argmin exact; alpha blend within one expf ulp
+    assert dg.max() <= 1 and (dg != 0).sum() <= max(2, 1e-3 * dg.size)   # argmin exact; alpha blend within one expf ulp
     d = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
     f.execute(dev(img), d)
     want = O.o_btf(img, k, nitr)
     got = d.cpu().numpy()
-    assert (got != want).mean() < 5e-3
+    assert (got != want).sum() <= max(6, 5e-3 * got.size)
 
 
 @settings(max_examples=15 * max(HUNT, 1), deadline=None, derandomize=not HUNT, suppress_health_check=SET["suppress_health_check"])
