@@ -187,6 +187,7 @@ def main():
     ap.add_argument("--workload", default="abf_4k_r7", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-threads", type=int, default=0, help="threads of the CPU baseline (0 = all host cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-probe", action="store_true", help="skip the issue-rate probe kernels (for ncu launch lists)")
     ap.add_argument("--content", default="rand", choices=["rand", "smooth"], help="synthetic content")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -357,7 +358,23 @@ def main():
     taps = mask_taps(radius if filt not in ("btf", "all") else ksize - 1)
     if filt in ("btf", "all"):
         alg_bytes = local_pixels * 9.0                    # dominant kernel = joint bilateral: src + guide in, dst out
-        kernel_ms = None                                  # several kernels per step: see profiles/ for the split
+        # several kernels per step: the dominant one (BTF's joint bilateral: ksize 2k-1, sigma_space k-1, sigma_color
+        # sqrt 3, src/bilateral_texture_filter_impl.cu:188) is timed alone, live, on the same resident frames (the
+        # filtered frame of the timed region serves as the guide), CUDA events on the launching stream
+        J = vip.CudaBilateralFilter(w, h, 2 * ksize - 1, float(ksize - 1), 3.0 ** 0.5)
+        d_tmp = torch.empty_like(d_dst[0])
+        jstep = lambda i: J.joint_bilateral_filter_async(d_src[i % n_pool], d_dst[i % n_pool], d_tmp)
+        for i in range(3):
+            jstep(i)
+        torch.cuda.synchronize()
+        jn = max(10, min(args.steps, 50))
+        j0, j1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        j0.record()
+        for i in range(jn):
+            jstep(i)
+        j1.record()
+        torch.cuda.synchronize()
+        kernel_ms = j0.elapsed_time(j1) / jn
         instr_per_tap = 8.5                               # JBF 17x17: smsp__inst_executed x 32 / taps (ncu, profiles/r01d)
         packed_per_tap = 2.0
         taps_per_px = taps * nitr + (2 * mask_taps(radius) if filt == "all" else 0)
@@ -375,17 +392,15 @@ def main():
     roof = {"bound": "hbm", "unit": "GB/s", "peak": hbm_peak, "peak_source": peak_src, "traffic": traffic,
             "kernel": {"bf": "stencil_kernel<BF>", "abf": "stencil_kernel<ABF>", "btf": "stencil_kernel<JBF>", "all": "stencil_kernel<JBF>"}[filt],
             "note": "the bilateral stencils are instruction-issue bound (see 'issue'); HBM traffic is 6-9 B/pixel"}
-    if kernel_ms:
-        roof["achieved"] = alg_bytes / (kernel_ms * 1e-3) / 1e9
-        roof["frac"] = roof["achieved"] / hbm_peak
-    else:
-        roof["achieved"] = alg_bytes * nitr / (ms_step * 1e-3) / 1e9
-        roof["frac"] = roof["achieved"] / hbm_peak
+    roof["achieved"] = alg_bytes / (kernel_ms * 1e-3) / 1e9
+    roof["frac"] = roof["achieved"] / hbm_peak
+    roof["kernel_ms"] = kernel_ms
     sm_mhz = clocks.get("sm_mhz") or float(peaks.get("sm_max_mhz", 1965.0))
     sm_count = torch.cuda.get_device_properties(local_rank).multi_processor_count
-    taps_s = local_pixels * taps_per_px / (ms_step * 1e-3)
+    taps_s = local_pixels * taps / (kernel_ms * 1e-3)    # of the dominant kernel, from its own live timing
     issue_peak = sm_count * 4 * 32 * sm_mhz * 1e6        # thread-instructions / s at the sampled clock
-    issue = {"taps_per_pixel": taps_per_px, "gtaps_per_s": taps_s / 1e9, "est_instr_per_tap": instr_per_tap,
+    issue = {"kernel": roof["kernel"], "kernel_ms": kernel_ms, "taps_per_pixel": taps, "step_taps_per_pixel": taps_per_px,
+             "gtaps_per_s": taps_s / 1e9, "est_instr_per_tap": instr_per_tap,
              "est_issue_util": taps_s * instr_per_tap / issue_peak, "sm_mhz_used": sm_mhz,
              "peak_thread_instr_per_s": issue_peak,
              "note": "taps/s x SASS instructions per tap (ncu smsp__inst_executed of the same kernel, profiles/) / (SMs x 4 x 32 x clock); packed fp32x2 instructions count once here but hold the dispatch port twice, see DESIGN.md 3"}
@@ -394,7 +409,7 @@ def main():
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         import peaks as _peaks
         _pl = _peaks.load()
-        if _pl is not None and rank == 0:
+        if _pl is not None and rank == 0 and not args.no_probe:
             ffma, _ = _peaks.measure(_pl, 0)
             ffma2, _ = _peaks.measure(_pl, 1)
             issue["measured_ffma_thread_instr_per_s"] = ffma
