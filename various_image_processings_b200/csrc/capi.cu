@@ -50,7 +50,7 @@ struct StencilTables {
     int last_nz = 0;    // last non-zero entry of the colour table
     int device = 0, sm_count = 0;
     std::vector<float> h_ks, h_lut;
-    DeviceBuf d_lut, d_hw, d_ks;
+    DeviceBuf d_lut, d_hw, d_ks, d_wrows;
 };
 
 int validate(int width, int height, int ksize, float ss, float sc) {
@@ -128,6 +128,14 @@ int init_tables(StencilTables& T, int width, int height, int ksize, float ss, fl
     if ((e = cudaMemcpy(T.d_ks.p, T.h_ks.data(), T.h_ks.size() * sizeof(float), cudaMemcpyHostToDevice)) !=
         cudaSuccess)
         return cu(e);
+    // the rows of the spatial kernel as the tiled kernels keep them in shared memory (one coalesced load per launch)
+    const int wp = vip::stencil_w_pitch(r);
+    std::vector<float> w_rows(static_cast<size_t>(ksize) * wp, 0.f);
+    for (int row = 0; row < ksize; row++)
+        for (int j = 0; j <= 2 * hw[row]; j++) w_rows[static_cast<size_t>(row) * wp + j] = T.h_ks[row * ksize + (r - hw[row] + j)];
+    if ((e = T.d_wrows.alloc(w_rows.size() * sizeof(float))) != cudaSuccess) return cu(e);
+    if ((e = cudaMemcpy(T.d_wrows.p, w_rows.data(), w_rows.size() * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess)
+        return cu(e);
     return VIP_OK;
 }
 
@@ -163,6 +171,7 @@ int run_stencil(const StencilTables& T, vip::StencilMode mode, const uint8_t* d_
     vip::stencil_pick_lut(mode, T.radius, T.table_len, T.last_nz, &a.lut_n, &a.lut_kind);
     a.hw = static_cast<const int*>(T.d_hw.p);
     a.ks_full = static_cast<const float*>(T.d_ks.p);
+    a.w_rows = static_cast<const float*>(T.d_wrows.p);
     return cu(vip::launch_stencil(mode, a, T.sm_count, static_cast<cudaStream_t>(stream)));
 }
 

@@ -27,12 +27,15 @@ struct StencilArgs {
     int lut_n;                  // entries replicated into shared memory
     int lut_kind;               // LutKind of stencil.cu: replication of the table and whether the index is clamped to lut_n-1
     const int* hw;              // device: 2r+1 half widths, hw[ky+r] = floor(sqrt(r^2-ky^2))
-    const float* ks_full;       // device: ksize*ksize spatial kernel (row ky: its 2*hw+1 non-zero weights are copied to shared memory)
+    const float* ks_full;       // device: ksize*ksize spatial kernel (the generic large-radius kernel reads it)
+    const float* w_rows;        // device: ksize rows of stencil_w_pitch(radius) floats: row ky = its 2*hw+1 non-zero weights from index 0, zero padded
 };
 
 cudaError_t launch_stencil(StencilMode mode, const StencilArgs& a, int sm_count, cudaStream_t stream);
 // Largest radius the tiled kernels cover; beyond it the generic one-thread-per-pixel kernel runs.
 int stencil_max_tiled_radius();
+// Floats per row of StencilArgs::w_rows.
+int stencil_w_pitch(int radius);
 // Decides how many colour-table entries are replicated in shared memory and whether the index is clamped.
 void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, int* lut_n, int* lut_kind);
 
