@@ -115,6 +115,8 @@ __global__ void __launch_bounds__(kThreads, 3) blur_rtv_kernel(const std::uint8_
     const int X0 = blockIdx.x * kTW;
     const int Y0 = out_y0 + blockIdx.y * kTH;
     const RowMap rowmap{H, src_y0, src_rows};
+    pdl_wait();     // launched through launch_pdl: the previous kernel of the stream has completed from here on
+    pdl_release();  // the next one may be scheduled as SMs free up
 
     // A. packed pixels of [X0-r-1, X0+kTW+r+1) x [Y0-r-1, Y0+kTH+r+1), coordinates clamped to the image
     //    interior tiles: 4 pixels per thread from aligned 32-bit loads; border tiles / leftover columns pixel by pixel
@@ -402,6 +404,8 @@ __global__ void __launch_bounds__(kThreads, 3) guide_kernel(const float* __restr
     const int X0 = blockIdx.x * kTW;
     const int Y0 = out_y0 + blockIdx.y * kTH;
     const RowMap rowmap{H, src_y0, src_rows};
+    pdl_wait();     // launched through launch_pdl: the previous kernel of the stream has completed from here on
+    pdl_release();  // the next one may be scheduled as SMs free up
 
     // The rtv tile and the blurred tile (+ radius halo) go to shared memory: the argmin pixel of every output lies inside
     // the tile, so the data-dependent gather of the reference (:168-175) becomes a shared-memory read.  Interior tiles
@@ -599,15 +603,15 @@ cudaError_t launch_blur_rtv_k(const std::uint8_t* image, const float* magnitude,
     if (magnitude) {
         e = cudaFuncSetAttribute(blur_rtv_kernel<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::total);
         if (e != cudaSuccess) return e;
-        blur_rtv_kernel<K, false><<<grid, kThreads, L::total, stream>>>(image, magnitude, blurred, rtv, W, H, src_y0,
-                                                                       src_rows, dst_y0, out_y0, out_rows);
+        e = launch_pdl(blur_rtv_kernel<K, false>, grid, dim3(kThreads), L::total, stream, image, magnitude, blurred, rtv, W, H,
+                       src_y0, src_rows, dst_y0, out_y0, out_rows);
     } else {
         e = cudaFuncSetAttribute(blur_rtv_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::total);
         if (e != cudaSuccess) return e;
-        blur_rtv_kernel<K, true><<<grid, kThreads, L::total, stream>>>(image, nullptr, blurred, rtv, W, H, src_y0,
-                                                                      src_rows, dst_y0, out_y0, out_rows);
+        e = launch_pdl(blur_rtv_kernel<K, true>, grid, dim3(kThreads), L::total, stream, image,
+                       static_cast<const float*>(nullptr), blurred, rtv, W, H, src_y0, src_rows, dst_y0, out_y0, out_rows);
     }
-    return cudaGetLastError();
+    return e;
 }
 
 template <int K>
@@ -617,9 +621,8 @@ cudaError_t launch_guide_k(const float* blurred, const float* rtv, std::uint8_t*
     const dim3 grid((W + kTW - 1) / kTW, (out_rows + kTH - 1) / kTH);
     cudaError_t e = cudaFuncSetAttribute(guide_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::total);
     if (e != cudaSuccess) return e;
-    guide_kernel<K><<<grid, kThreads, L::total, stream>>>(blurred, rtv, guide, W, H, src_y0, src_rows, dst_y0, out_y0,
-                                                         out_rows);
-    return cudaGetLastError();
+    return launch_pdl(guide_kernel<K>, grid, dim3(kThreads), L::total, stream, blurred, rtv, guide, W, H, src_y0, src_rows,
+                      dst_y0, out_y0, out_rows);
 }
 
 }  // namespace

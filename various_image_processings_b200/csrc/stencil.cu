@@ -30,6 +30,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
 #include <type_traits>
 
 #include "vip_internal.h"
@@ -437,6 +438,11 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
         fill_tables<LK>(a.lut, a.lut_n, a.w_rows, a.hw, k, lut_s, w_s, hw_s, k * L.w_pitch);
     constexpr int kRepLog2 = lut_shift(LK) - 2;  // copies per entry (log2)
     if (threadIdx.x == 0) sched[0] = 0;
+    // Programmatic dependent launch: the prologue above touches only this filter's constant tables, so it may run while
+    // the previous kernel of the stream is still draining; everything below reads / writes images and waits for it.
+    // The next kernel may be scheduled as soon as SMs free up (no-ops when launched without the attribute).
+    pdl_wait();
+    pdl_release();
     __syncthreads();
 
     // byte address of this lane's copy of entry 0; ABF folds the 2^23 bias of its index trick in (see run_taps)
@@ -741,9 +747,9 @@ cudaError_t launch_tiled(const StencilArgs& a, int sm_count, cudaStream_t stream
     // one persistent CTA per SM
     int grid = sm_count;
     if (grid > n_tiles) grid = n_tiles;
-    kern<<<grid, kThreads * n_groups, L.total, stream>>>(a, tiles_x, n_tiles);
+    e = launch_pdl(kern, dim3(grid), dim3(kThreads * n_groups), L.total, stream, a, tiles_x, n_tiles);
     count_launch();
-    return cudaGetLastError();
+    return e;
 }
 
 template <int MODE>

@@ -8,9 +8,45 @@
 #include <cstddef>
 #include <cstdint>
 
+#include <cstdlib>
+
 namespace vip {
 
 enum StencilMode { kBF = 0, kJBF = 1, kABF = 2 };
+
+// Programmatic dependent launch (sm_90+).  Kernels launched through launch_pdl() may be SCHEDULED while the previous
+// kernel of the stream drains (launch latency and constant-table prologues overlap its tail); each of them executes
+// pdl_wait() before it touches any image buffer, which blocks until the previous grid has completed and flushed, and
+// pdl_release() to let its own successor be scheduled early.  Both are no-ops in a normally launched grid.
+// VIP_PDL=0 in the environment launches everything the classic way (A/B measurements).
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_release() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+inline bool pdl_enabled() {
+    static const bool on = [] {
+        const char* v = std::getenv("VIP_PDL");
+        return !(v && v[0] == '0');
+    }();
+    return on;
+}
+
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+    return e != cudaSuccess ? e : cudaGetLastError();
+}
+#endif
 
 // Arguments of the bilateral-family stencil kernels (stencil.cu).  Row numbers are rows of the FULL image;
 // the buffers hold the rows a strip describes (include/vip_c_api.h, struct vip_strip).
