@@ -46,7 +46,7 @@ def dev(a):
 
 sizes = st.tuples(st.integers(1, 150), st.integers(1, 90))
 kinds = st.sampled_from(["rand", "narrow", "const", "extreme", "smooth"])
-odd_k = st.integers(0, 10).map(lambda r: 2 * r + 1)
+odd_k = st.integers(0, 20).map(lambda r: 2 * r + 1)        # radius <= 15: tiled kernels, beyond: the generic kernel
 sigma = st.floats(0.5, 200.0, allow_nan=False, allow_infinity=False, width=32)
 
 
@@ -194,3 +194,35 @@ def test_multigpu_strips_random_cases(vip, n, h, w, kind, k, nitr, mode, seed):
     else:
         vip.CudaBilateralTextureFilter(w, h, k, nitr).execute(dev(img), d)
     assert np.array_equal(got, d.cpu().numpy())
+
+
+@settings(max_examples=20 * max(HUNT, 1), deadline=None, derandomize=not HUNT, suppress_health_check=SET["suppress_health_check"])
+@given(w=st.integers(4, 120), h=st.integers(20, 150), k=st.sampled_from([3, 5, 9]), a=st.floats(0, 1), b=st.floats(0, 1),
+       slack=st.tuples(st.integers(0, 9), st.integers(0, 9)), kind=st.sampled_from(["jbf", "btf", "grad"]), seed=st.integers(0, 10**6))
+def test_strip_calls_random_row_ranges(vip, w, h, k, a, b, slack, kind, seed):
+    """Any output row range [y0, y1) from buffers that hold exactly the rows it needs (+ random slack): joint bilateral,
+    one BTF iteration and the gradient write the same rows a whole-image call produces (the contract of struct vip_strip)."""
+    img, guide = make_image(w, h, "rand", seed), make_image(w, h, "smooth", seed + 1)
+    y0, y1 = sorted((int(a * h), int(b * h)))
+    y1 = min(h, max(y1, y0 + 1))
+    f_btf = vip.CudaBilateralTextureFilter(w, h, k, 1)
+    halo = {"jbf": k // 2, "btf": f_btf.halo_rows_per_iteration(), "grad": 1}[kind]
+    s0, s1 = max(0, y0 - halo - slack[0]), min(h, y1 + halo + slack[1])
+    strip = vip.Strip(s0, s1 - s0, y0, y0, y1 - y0)
+    if kind == "grad":
+        whole = torch.empty((h, w), dtype=torch.float32, device="cuda")
+        vip.cuda_gradient(dev(img), whole, w, h, 3)
+        part = torch.full((y1 - y0, w), -1.0, dtype=torch.float32, device="cuda")
+        vip.cuda_gradient_strip(dev(img[s0:s1]), part, w, h, 3, strip)
+    else:
+        whole = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+        part = torch.empty((y1 - y0, w, 3), dtype=torch.uint8, device="cuda")
+        if kind == "jbf":
+            F = vip.CudaBilateralFilter(w, h, k)
+            F.joint_bilateral_filter(dev(img), dev(guide), whole)
+            F.joint_bilateral_filter_strip(dev(img[s0:s1]), dev(guide[s0:s1]), part, strip)
+        else:
+            f_btf.execute(dev(img), whole)                       # nitr = 1: one iteration
+            vip.CudaBilateralTextureFilter(w, h, k, 1).iterate_strip(dev(img[s0:s1]), part, strip)
+    torch.cuda.synchronize()
+    assert torch.equal(part, whole[y0:y1])
