@@ -79,6 +79,18 @@ VIP_API const char* vip_status_string(int status);
 /* Number of kernels this library has launched in the calling process (all threads), for benchmark
  * accounting ("gpu_launches"). */
 VIP_API unsigned long long vip_launch_count(void);
+/* How a bilateral-family filter with these parameters will run on the device -- pure host logic, no CUDA call, so
+ * it also answers on a machine without a GPU (the tests sweep it to prove that every valid parameter set has a launch
+ * configuration).  mode: 0 bilateral, 1 joint bilateral, 2 adaptive bilateral. */
+typedef struct vip_stencil_plan {
+    int tiled;        /* 1: persistent tiled kernel (radius <= 15); 0: one-thread-per-pixel kernel                 */
+    int lut_entries;  /* range-table entries kept in shared memory (the all-zero tail may be cut)                  */
+    int lut_copies;   /* copies of every entry: 32 (bank-conflict free for any content) or 8                       */
+    int lut_clamped;  /* 1: the index is clamped to lut_entries - 1                                                */
+    int warp_groups;  /* 256-thread warp groups per CTA (one CTA per SM)                                           */
+    int smem_bytes;   /* dynamic shared memory per CTA                                                             */
+} vip_stencil_plan;
+VIP_API int vip_stencil_plan_query(int mode, int ksize, float sigma_space, float sigma_color, vip_stencil_plan* out);
 
 /* ---- device image container ---------------------------------------------------------------------------
  * replaces DeviceImage<ElemType> (include/cuda/device_image.hpp:4-16, src/device_image.cu:5-52).

@@ -107,3 +107,35 @@ def test_division_by_constant_shortcut_is_exact(tmp_path):
     subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", os.path.join(ROOT, "tests", "div_const_check.c"), "-o", str(exe), "-lm"])
     out = subprocess.check_output([str(exe)], text=True)
     assert "mismatches 0" in out
+
+
+def test_every_valid_filter_has_a_launch_configuration():
+    """vip_stencil_plan_query is pure host logic: sweep window sizes 1..41 x sigma_color 0.5..1000 x the three filters and
+    require a configuration that fits the 227 KB of shared memory of an SM.  (ABF with sigma_color >~ 50 once had none:
+    1536 non-zero table entries x 32 copies = 192 KB; it now runs with 8 copies.)"""
+    import ctypes as C
+    import various_image_processings_b200 as vip
+    L = vip.capi.lib()
+    seen = set()
+    for mode in (0, 1, 2):
+        for k in range(1, 43, 2):
+            for sc in (0.5, 1.7320508, 5.0, 30.0, 50.0, 60.0, 106.0, 200.0, 400.0, 1000.0):
+                plan = vip.capi.StencilPlan()
+                assert L.vip_stencil_plan_query(mode, k, 10.0, sc, C.byref(plan)) == vip.capi.VIP_OK
+                if k // 2 > 15:
+                    assert plan.tiled == 0
+                    continue
+                assert plan.tiled == 1 and plan.warp_groups >= 1, (mode, k, sc)
+                assert 0 < plan.smem_bytes <= 227 * 1024, (mode, k, sc, plan.smem_bytes)
+                assert plan.lut_copies in (8, 32) and 2 <= plan.lut_entries <= (1536 if mode == 2 else 768)
+                seen.add((plan.lut_copies, plan.lut_clamped))
+    assert seen == {(32, 0), (32, 1), (8, 1)}           # all three table layouts occur
+    # the configured workloads keep three warp groups and a conflict-free table
+    for mode, k, ss, sc in ((0, 11, 10.0, 30.0), (2, 15, 10.0, 30.0), (1, 17, 8.0, 1.7320508), (0, 31, 10.0, 30.0)):
+        plan = vip.capi.StencilPlan()
+        assert L.vip_stencil_plan_query(mode, k, ss, sc, C.byref(plan)) == 0
+        assert (plan.warp_groups, plan.lut_copies) == (3, 32), (mode, k, plan.warp_groups, plan.lut_copies)
+    bad = vip.capi.StencilPlan()
+    assert L.vip_stencil_plan_query(0, 8, 10.0, 30.0, C.byref(bad)) == vip.capi.VIP_E_KSIZE
+    assert L.vip_stencil_plan_query(3, 9, 10.0, 30.0, C.byref(bad)) == vip.capi.VIP_E_UNSUPPORTED
+    assert L.vip_stencil_plan_query(0, 9, 10.0, 30.0, None) == vip.capi.VIP_E_NULL

@@ -12,6 +12,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("VIP_B200_LIB") or os.path.join(_HERE, "lib", "libvip_b200.so")
 
 VIP_OK = 0
+(VIP_E_NULL, VIP_E_SIZE, VIP_E_KSIZE, VIP_E_SIGMA, VIP_E_STRIP, VIP_E_ALLOC, VIP_E_UNSUPPORTED,
+ VIP_E_DEVICE) = range(-1, -9, -1)
 VIP_LUT_CUDA, VIP_LUT_CPU = 0, 1
 VIP_MG_BF, VIP_MG_ABF, VIP_MG_BTF = 0, 1, 2
 VIP_MG_FLAG_BTF_EXCHANGE, VIP_MG_FLAG_BTF_DEEP_HALO = 1, 2
@@ -30,6 +32,12 @@ class Strip(C.Structure):
                 ("out_rows", C.c_int)]
 
 
+class StencilPlan(C.Structure):
+    """struct vip_stencil_plan: how a bilateral-family filter will run (host logic, answers without a GPU)."""
+    _fields_ = [("tiled", C.c_int), ("lut_entries", C.c_int), ("lut_copies", C.c_int), ("lut_clamped", C.c_int),
+                ("warp_groups", C.c_int), ("smem_bytes", C.c_int)]
+
+
 _vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
 _pp = C.POINTER(C.c_void_p)
 
@@ -38,6 +46,7 @@ SIGNATURES = {
     "vip_version": (C.c_char_p, []),
     "vip_status_string": (C.c_char_p, [_i]),
     "vip_launch_count": (C.c_ulonglong, []),
+    "vip_stencil_plan_query": (_i, [_i, _i, _f, _f, C.POINTER(StencilPlan)]),
     "vip_image_create": (_i, [_pp, _i, _i, _i, _i]),
     "vip_image_destroy": (_i, [_vp]),
     "vip_image_upload": (_i, [_vp, _vp]),

@@ -217,6 +217,28 @@ const char* vip_status_string(int status) {
 
 unsigned long long vip_launch_count(void) { return vip::g_launches.load(std::memory_order_relaxed); }
 
+int vip_stencil_plan_query(int mode, int ksize, float sigma_space, float sigma_color, vip_stencil_plan* out) {
+    if (!out) return VIP_E_NULL;
+    if (mode < 0 || mode > 2) return VIP_E_UNSUPPORTED;
+    const int v = validate(1, 1, ksize, sigma_space, sigma_color);
+    if (v != VIP_OK) return v;
+    const int table_len = mode == 2 ? 1536 : 768;
+    std::vector<float> ks, lut;
+    build_luts(ksize, sigma_space, sigma_color, table_len, VIP_LUT_CUDA, ks, lut);
+    int last_nz = table_len - 1;
+    while (last_nz > 0 && lut[last_nz] == 0.f) last_nz--;
+    const int radius = ksize / 2;
+    int lut_n = table_len, kind = 0;
+    vip::stencil_pick_lut(static_cast<vip::StencilMode>(mode), radius, table_len, last_nz, &lut_n, &kind);
+    std::memset(out, 0, sizeof(*out));
+    out->tiled = radius <= vip::stencil_max_tiled_radius() ? 1 : 0;
+    out->lut_entries = lut_n;
+    if (out->tiled)
+        vip::stencil_describe(static_cast<vip::StencilMode>(mode), radius, lut_n, kind, &out->lut_copies, &out->lut_clamped,
+                              &out->warp_groups, &out->smem_bytes);
+    return VIP_OK;
+}
+
 /* ---------------------------------------------------------------- images */
 int vip_image_create(vip_image** out, int width, int height, int channels, int elem_size) {
     if (!out) return VIP_E_NULL;

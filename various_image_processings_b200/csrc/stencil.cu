@@ -776,6 +776,15 @@ int stencil_max_tiled_radius() { return kMaxTiledRadius; }
 
 int stencil_w_pitch(int radius) { return (2 * radius + 1 + 7) & ~7; }
 
+void stencil_describe(StencilMode mode, int radius, int lut_n, int lut_kind, int* copies, int* clamped, int* groups,
+                      int* smem_bytes) {
+    const int g = groups_that_fit(mode, radius, lut_n, lut_kind);
+    *copies = 1 << (lut_shift(lut_kind) - 2);
+    *clamped = lut_clamped(lut_kind) ? 1 : 0;
+    *groups = g;
+    *smem_bytes = g > 0 ? make_layout(mode, outputs_per_thread(mode), radius, lut_n, lut_kind, g).total : 0;
+}
+
 void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, int* lut_n, int* lut_kind) {
     // The table is shared by the warp groups of the one CTA an SM runs.  Candidates, in order of preference at an equal
     // number of warp groups: the whole table 32x replicated (no clamp instruction); the table cut after its last

@@ -70,6 +70,9 @@ struct StencilArgs {
 cudaError_t launch_stencil(StencilMode mode, const StencilArgs& a, int sm_count, cudaStream_t stream);
 // Largest radius the tiled kernels cover; beyond it the generic one-thread-per-pixel kernel runs.
 int stencil_max_tiled_radius();
+// Launch configuration of the tiled kernels for a table of `lut_n` entries of kind `lut_kind` (host logic only).
+void stencil_describe(StencilMode mode, int radius, int lut_n, int lut_kind, int* copies, int* clamped, int* groups,
+                      int* smem_bytes);
 // Floats per row of StencilArgs::w_rows.
 int stencil_w_pitch(int radius);
 // Decides how many colour-table entries are replicated in shared memory and whether the index is clamped.
