@@ -242,6 +242,16 @@ VIP_API int vip_mg_create_ex(vip_mg** out, const int* device_ids, int n_devices,
 VIP_API int vip_mg_destroy(vip_mg* m);
 /* Row range [*y0, *y0 + *rows) owned by device slot `i`. */
 VIP_API int vip_mg_strip_rows(const vip_mg* m, int i, int* y0, int* rows);
+/* The strip plan vip_mg_create_ex would make, as pure host logic (no CUDA call, no devices needed): what slot `i`
+ * of `n_devices` owns, what its buffers hold, and for BTF which halo mode was chosen. */
+typedef struct vip_mg_plan {
+    int y0, rows;          /* rows owned (and produced) by the slot                                               */
+    int buf_y0, buf_rows;  /* rows held by its strip buffers: owned rows + halo rows on each side, clipped         */
+    int halo;              /* halo rows ONE pass needs on each side: radius, or (k-1) + 2 (k/2) + 1 per BTF iteration */
+    int btf_deep_halo;     /* BTF: 1 = the buffers carry nitr x halo rows and the overlap is recomputed, 0 = exchange */
+} vip_mg_plan;
+VIP_API int vip_mg_plan_query(int n_devices, int slot, int kind, int height, int ksize, int nitr, int flags,
+                              vip_mg_plan* out);
 /* Scatter a full host image (pinned or pageable) into the per-device strip buffers (own rows + halos). */
 VIP_API int vip_mg_scatter_host(vip_mg* m, const uint8_t* h_src);
 /* Scatter from a full image resident on device slot 0 using peer copies. */

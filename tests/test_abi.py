@@ -139,3 +139,56 @@ def test_every_valid_filter_has_a_launch_configuration():
     assert L.vip_stencil_plan_query(0, 8, 10.0, 30.0, C.byref(bad)) == vip.capi.VIP_E_KSIZE
     assert L.vip_stencil_plan_query(3, 9, 10.0, 30.0, C.byref(bad)) == vip.capi.VIP_E_UNSUPPORTED
     assert L.vip_stencil_plan_query(0, 9, 10.0, 30.0, None) == vip.capi.VIP_E_NULL
+
+
+def test_multigpu_strip_plan_invariants():
+    """vip_mg_plan_query (host logic of csrc/mg.cu): the strips tile the image; every pass finds its halo rows in the
+    buffers; with deep halos iteration `it` can produce owned rows +- (nitr-1-it) x halo from what iteration it-1 produced;
+    with the exchange every neighbour owns enough rows to serve a halo."""
+    import ctypes as C
+    import random
+    import various_image_processings_b200 as vip
+    L, cap = vip.capi.lib(), vip.capi
+    rnd = random.Random(7)
+    modes_seen = set()
+    for _ in range(3000):
+        n, h = rnd.randint(1, 8), rnd.randint(1, 5000)
+        kind = rnd.choice([cap.VIP_MG_BF, cap.VIP_MG_ABF, cap.VIP_MG_BTF])
+        k, nitr = rnd.choice([1, 3, 5, 9, 15, 31]), rnd.randint(0, 4)
+        flags = rnd.choice([0, cap.VIP_MG_FLAG_BTF_EXCHANGE, cap.VIP_MG_FLAG_BTF_DEEP_HALO])
+        plans, rc = [], 0
+        for i in range(n):
+            p = cap.MgPlan()
+            rc = L.vip_mg_plan_query(n, i, kind, h, k, nitr, flags, C.byref(p))
+            if rc != 0:
+                break
+            plans.append(p)
+        halo = (k - 1) + 2 * (k // 2) + 1 if kind == cap.VIP_MG_BTF else k // 2
+        if rc != 0:
+            # the only refusal for valid arguments: BTF halo exchange with strips too thin to serve a neighbour's halo
+            assert rc == cap.VIP_E_SIZE and kind == cap.VIP_MG_BTF and n > 1 and nitr > 1 and h // n < halo
+            assert flags != cap.VIP_MG_FLAG_BTF_DEEP_HALO
+            continue
+        assert plans[0].y0 == 0 and plans[-1].y0 + plans[-1].rows == h
+        deep = plans[0].btf_deep_halo
+        modes_seen.add((kind == cap.VIP_MG_BTF, deep))
+        for i, p in enumerate(plans):
+            assert p.halo == halo and p.btf_deep_halo == deep and p.rows >= 0
+            if i:
+                assert p.y0 == plans[i - 1].y0 + plans[i - 1].rows                  # contiguous, no overlap
+            b0, b1 = p.buf_y0, p.buf_y0 + p.buf_rows
+            assert 0 <= b0 <= p.y0 and p.y0 + p.rows <= b1 <= h
+            if kind != cap.VIP_MG_BTF or not deep:
+                assert b0 == max(0, p.y0 - halo) and b1 == min(h, p.y0 + p.rows + halo)
+                if n > 1 and kind == cap.VIP_MG_BTF and nitr > 1:
+                    assert p.rows >= halo                                            # can serve a neighbour's halo
+            else:
+                assert flags != cap.VIP_MG_FLAG_BTF_EXCHANGE and nitr > 1 and n > 1
+                have = (b0, b1)                                                      # rows valid in the input of iteration 0
+                for it in range(nitr):
+                    m = (nitr - 1 - it) * halo
+                    o0, o1 = max(0, p.y0 - m), min(h, p.y0 + p.rows + m)             # what csrc/mg.cu asks iteration `it` for
+                    assert have[0] <= max(0, o0 - halo) and min(h, o1 + halo) <= have[1]
+                    have = (o0, o1)
+                assert have == (p.y0, p.y0 + p.rows)
+    assert modes_seen == {(False, 0), (True, 0), (True, 1)}

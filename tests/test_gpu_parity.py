@@ -512,6 +512,18 @@ def test_multigpu_btf_halo_modes(vip, mode, n, h, nitr, k):
     assert np.array_equal(mg.execute(img), run_btf(vip, img, k, nitr))       # a second run on the same object
 
 
+@pytest.mark.parametrize("kind,k,nitr,h", [("bf", 31, 0, 20), ("abf", 15, 0, 5), ("btf", 9, 1, 6), ("btf", 5, 3, 30), ("bf", 9, 0, 3)])
+def test_multigpu_thin_strips(vip, kind, k, nitr, h):
+    """Eight slots on an image with fewer rows than a halo (or than slots): BF / ABF / one BTF iteration take their halos
+    from the scattered source, BTF with several iterations falls to deep halos; slots that own no row do nothing."""
+    w, n = 70, 8
+    img = O.rand_image(w, h, seed=h + k)
+    mg = vip.MultiGpuFilter([i % torch.cuda.device_count() for i in range(n)], kind, w, h, ksize=k, nitr=nitr,
+                            btf_halo="deep" if nitr > 1 else None)
+    want = {"bf": lambda: run_bf(vip, img, k), "abf": lambda: run_abf(vip, img, k), "btf": lambda: run_btf(vip, img, k, nitr)}[kind]()
+    assert np.array_equal(mg.execute(img), want)
+
+
 def test_multigpu_driver_many_slots_create_destroy(vip):
     """8 slots (the 8 x B200 box) on whatever devices exist: the worker threads start / stop cleanly, repeatedly."""
     n = torch.cuda.device_count()

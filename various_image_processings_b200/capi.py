@@ -38,6 +38,12 @@ class StencilPlan(C.Structure):
                 ("warp_groups", C.c_int), ("smem_bytes", C.c_int)]
 
 
+class MgPlan(C.Structure):
+    """struct vip_mg_plan: rows a device slot owns / holds and the BTF halo mode (host logic, answers without a GPU)."""
+    _fields_ = [("y0", C.c_int), ("rows", C.c_int), ("buf_y0", C.c_int), ("buf_rows", C.c_int), ("halo", C.c_int),
+                ("btf_deep_halo", C.c_int)]
+
+
 _vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
 _pp = C.POINTER(C.c_void_p)
 
@@ -95,6 +101,7 @@ SIGNATURES = {
     "vip_btf_scratch_bytes": (_sz, [_vp]),
     "vip_mg_create": (_i, [_pp, C.POINTER(C.c_int), _i, _i, _i, _i, _i, _f, _f, _i]),
     "vip_mg_create_ex": (_i, [_pp, C.POINTER(C.c_int), _i, _i, _i, _i, _i, _f, _f, _i, _i]),
+    "vip_mg_plan_query": (_i, [_i, _i, _i, _i, _i, _i, _i, C.POINTER(MgPlan)]),
     "vip_mg_destroy": (_i, [_vp]),
     "vip_mg_strip_rows": (_i, [_vp, _i, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "vip_mg_scatter_host": (_i, [_vp, _vp]),

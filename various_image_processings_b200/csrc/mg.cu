@@ -121,6 +121,34 @@ int run_one(vip_mg* m, Slot& s, const uint8_t* src, uint8_t* dst, const vip_stri
     }
 }
 
+// The strip plan (host logic only; vip_mg_plan_query exposes it so that it can be checked without devices).
+int plan_slot(int n_devices, int slot, int kind, int height, int ksize, int nitr, int flags, vip_mg_plan* out) {
+    if (n_devices < 1 || n_devices > 64 || slot < 0 || slot >= n_devices) return VIP_E_DEVICE;
+    if (kind != VIP_MG_BF && kind != VIP_MG_ABF && kind != VIP_MG_BTF) return VIP_E_UNSUPPORTED;
+    if (height <= 0) return VIP_E_SIZE;
+    if (ksize < 1 || (ksize & 1) == 0) return VIP_E_KSIZE;
+    if (kind == VIP_MG_BTF && nitr < 0) return VIP_E_UNSUPPORTED;
+    if ((flags & VIP_MG_FLAG_BTF_EXCHANGE) && (flags & VIP_MG_FLAG_BTF_DEEP_HALO)) return VIP_E_UNSUPPORTED;
+    const int halo = (kind == VIP_MG_BTF) ? (ksize - 1) + 2 * (ksize / 2) + 1 : ksize / 2;
+    bool deep = false;
+    if (kind == VIP_MG_BTF && n_devices > 1 && nitr > 1) {
+        // redundant rows of the deep-halo mode, averaged over the iterations: (nitr-1) x halo per strip
+        const long long extra = static_cast<long long>(nitr - 1) * halo, strip = height / n_devices;
+        deep = (flags & VIP_MG_FLAG_BTF_DEEP_HALO) || (!(flags & VIP_MG_FLAG_BTF_EXCHANGE) && extra * 100 <= strip * 35);
+    }
+    // BTF halo exchange: every strip must be able to serve its neighbour's halo from its own rows (BF / ABF and the
+    // deep-halo mode take their halos from the scattered source, any strip height works)
+    if (kind == VIP_MG_BTF && n_devices > 1 && nitr > 1 && !deep && height / n_devices < halo) return VIP_E_SIZE;
+    const int buf_halo = deep ? nitr * halo : halo;  // rows the strip buffers carry on each side
+    out->y0 = static_cast<int>(static_cast<long long>(height) * slot / n_devices);
+    out->rows = static_cast<int>(static_cast<long long>(height) * (slot + 1) / n_devices) - out->y0;
+    out->buf_y0 = std::max(0, out->y0 - buf_halo);
+    out->buf_rows = std::min(height, out->y0 + out->rows + buf_halo) - out->buf_y0;
+    out->halo = halo;
+    out->btf_deep_halo = deep ? 1 : 0;
+    return VIP_OK;
+}
+
 // Everything slot i contributes to one run, enqueued on its stream by its worker thread.
 int enqueue_slot(vip_mg* m, int i) {
     Slot& s = m->slots[i];
@@ -129,9 +157,11 @@ int enqueue_slot(vip_mg* m, int i) {
     if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
     if ((e = cudaEventRecord(s.ev_start, s.stream)) != cudaSuccess) return cu(e);
     if (m->kind != VIP_MG_BTF) {
-        const vip_strip st{s.sy0, s.srows, s.y0, s.y0, s.rows};
-        const int rc = run_one(m, s, s.src, s.buf[0], st);
-        if (rc != VIP_OK) return rc;
+        if (s.rows > 0) {  // more slots than image rows: this one owns nothing
+            const vip_strip st{s.sy0, s.srows, s.y0, s.y0, s.rows};
+            const int rc = run_one(m, s, s.src, s.buf[0], st);
+            if (rc != VIP_OK) return rc;
+        }
     } else {
         auto wait_recorded = [&](int j, int want) {  // the neighbour's event must be RECORDED before it can be waited on
             while (m->iter_recorded[j].load(std::memory_order_acquire) < want) std::this_thread::yield();
@@ -242,17 +272,11 @@ int vip_mg_create_ex(vip_mg** out, const int* device_ids, int n_devices, int kin
     if (e != cudaSuccess) return cu(e);
     for (int i = 0; i < n_devices; i++)
         if (device_ids[i] < 0 || device_ids[i] >= ndev) return VIP_E_DEVICE;
-    const int halo = (kind == VIP_MG_BTF) ? (ksize - 1) + 2 * (ksize / 2) + 1 : ksize / 2;
-    if ((flags & VIP_MG_FLAG_BTF_EXCHANGE) && (flags & VIP_MG_FLAG_BTF_DEEP_HALO)) return VIP_E_UNSUPPORTED;
-    bool deep = false;
-    if (kind == VIP_MG_BTF && n_devices > 1 && nitr > 1) {
-        // redundant rows of the deep-halo mode, averaged over the iterations: (nitr-1) x halo per strip
-        const long long extra = static_cast<long long>(nitr - 1) * halo, strip = height / n_devices;
-        deep = (flags & VIP_MG_FLAG_BTF_DEEP_HALO) || (!(flags & VIP_MG_FLAG_BTF_EXCHANGE) && extra * 100 <= strip * 35);
-    }
-    // exchange mode: every strip must be able to serve a neighbour's halo from its own rows
-    if (n_devices > 1 && !deep && height / n_devices < halo) return VIP_E_SIZE;
-    const int buf_halo = deep ? nitr * halo : halo;   // rows the strip buffers carry on each side
+    vip_mg_plan plan0;
+    const int prc = plan_slot(n_devices, 0, kind, height, ksize, nitr, flags, &plan0);
+    if (prc != VIP_OK) return prc;
+    const int halo = plan0.halo;
+    const bool deep = plan0.btf_deep_halo != 0;
 
     DeviceGuard guard;
     vip_mg* m = new (std::nothrow) vip_mg();
@@ -273,10 +297,12 @@ int vip_mg_create_ex(vip_mg** out, const int* device_ids, int n_devices, int kin
     for (int i = 0; i < n_devices && rc == VIP_OK; i++) {
         Slot& s = m->slots[i];
         s.device = device_ids[i];
-        s.y0 = static_cast<int>(static_cast<long long>(height) * i / n_devices);
-        s.rows = static_cast<int>(static_cast<long long>(height) * (i + 1) / n_devices) - s.y0;
-        s.sy0 = std::max(0, s.y0 - buf_halo);
-        s.srows = std::min(height, s.y0 + s.rows + buf_halo) - s.sy0;
+        vip_mg_plan pl;
+        plan_slot(n_devices, i, kind, height, ksize, nitr, flags, &pl);
+        s.y0 = pl.y0;
+        s.rows = pl.rows;
+        s.sy0 = pl.buf_y0;
+        s.srows = pl.buf_rows;
         if ((e = cudaSetDevice(s.device)) != cudaSuccess) { rc = cu(e); break; }
         // P2P with the neighbouring slots (an error only means "already enabled" or "not supported":
         // cudaMemcpyPeerAsync then falls back to staging through the host)
@@ -322,6 +348,11 @@ int vip_mg_create_ex(vip_mg** out, const int* device_ids, int n_devices, int kin
     for (int i = 0; i < n_devices; i++) m->workers[i]->th = std::thread(worker_main, m, m->workers[i].get(), i);
     *out = m;
     return VIP_OK;
+}
+
+int vip_mg_plan_query(int n_devices, int slot, int kind, int height, int ksize, int nitr, int flags, vip_mg_plan* out) {
+    if (!out) return VIP_E_NULL;
+    return plan_slot(n_devices, slot, kind, height, ksize, nitr, flags, out);
 }
 
 int vip_mg_destroy(vip_mg* m) {
@@ -419,6 +450,7 @@ int vip_mg_gather_host(vip_mg* m, uint8_t* h_dst) {
         if (m->kind != VIP_MG_BTF) from = s.buf[0];
         else if (m->result_buf < 0) from = s.src + row_bytes * (s.y0 - s.sy0);
         else from = s.buf[m->result_buf] + row_bytes * (s.y0 - s.sy0);
+        if (s.rows == 0) continue;
         e = cudaMemcpyAsync(h_dst + row_bytes * s.y0, from, row_bytes * s.rows, cudaMemcpyDeviceToHost, s.stream);
         if (e != cudaSuccess) return cu(e);
     }
