@@ -188,8 +188,11 @@ private:
 class VIP_API MultiGpuFilter {
 public:
     enum Kind { Bilateral = VIP_MG_BF, AdaptiveBilateral = VIP_MG_ABF, BilateralTexture = VIP_MG_BTF };
+    // BilateralTexture strips: deep halos (nitr x 17 rows from the scatter, overlap recomputed, no communication) or a
+    // peer-to-peer halo exchange after every iteration; Automatic = deep while the redundant rows are <= 35 % of a strip
+    enum BtfHalo { Automatic = 0, Exchange = VIP_MG_FLAG_BTF_EXCHANGE, DeepHalo = VIP_MG_FLAG_BTF_DEEP_HALO };
     MultiGpuFilter(const std::vector<int>& device_ids, Kind kind, int width, int height, int ksize = 9,
-                   float sigma_space = 10.f, float sigma_color = 30.f, int nitr = 3);
+                   float sigma_space = 10.f, float sigma_color = 30.f, int nitr = 3, BtfHalo btf_halo = Automatic);
     ~MultiGpuFilter();
     MultiGpuFilter(const MultiGpuFilter&) = delete;
     MultiGpuFilter& operator=(const MultiGpuFilter&) = delete;

@@ -197,10 +197,10 @@ const std::uint32_t* CudaIntegralImage::table() const { return static_cast<const
 
 // ---------------------------------------------------------------- MultiGpuFilter
 MultiGpuFilter::MultiGpuFilter(const std::vector<int>& device_ids, Kind kind, int width, int height, int ksize,
-                               float sigma_space, float sigma_color, int nitr)
+                               float sigma_space, float sigma_color, int nitr, BtfHalo btf_halo)
     : handle_(nullptr) {
-    VIP_CHECK(vip_mg_create(&handle_, device_ids.data(), static_cast<int>(device_ids.size()), static_cast<int>(kind), width,
-                            height, ksize, sigma_space, sigma_color, nitr));
+    VIP_CHECK(vip_mg_create_ex(&handle_, device_ids.data(), static_cast<int>(device_ids.size()), static_cast<int>(kind),
+                               width, height, ksize, sigma_space, sigma_color, nitr, static_cast<int>(btf_halo)));
 }
 MultiGpuFilter::~MultiGpuFilter() { vip_mg_destroy(handle_); }
 void MultiGpuFilter::execute(const std::uint8_t* h_src, std::uint8_t* h_dst) {
