@@ -420,6 +420,10 @@ def main():
             issue["packed_instr_per_tap"] = packed_per_tap
             issue["dispatch_slots_per_tap"] = instr_per_tap + packed_per_tap
             issue["frac_of_measured_issue_roof"] = taps_s * (instr_per_tap + packed_per_tap) / ffma
+            # the same inside the roofline object, for a reader who looks only there: the bound that binds this kernel
+            roof["relevant"] = {"bound": "issue", "unit": "thread-instr/s", "achieved": taps_s * (instr_per_tap + packed_per_tap),
+                                "peak": ffma, "peak_source": "measured live (tools/probe/issue_probe.cu, FFMA)",
+                                "frac": issue["frac_of_measured_issue_roof"]}
     except Exception as exc:                                 # the probe is optional evidence, never a reason to fail the bench
         issue["probe_error"] = str(exc)
 
