@@ -2,20 +2,25 @@
 """Benchmark of the edge-preserving-filter hot path (BASELINE.json).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+                  [--content rand|narrow|nat|smooth] [--halo fused|copy] [--no-per-workload]
 
-Default workload (N = 1): BASELINE.json configs[1] -- adaptive bilateral filter, radius 7 (ksize 15), on a synthetic
-3840x2160 RGB image, one B200.  A "step" is one pass of the filter over one frame.  At N > 1 (torchrun, one process
-per GPU) every rank filters its own frames (frames are independent: no data-path collective, weak scaling) and the
-time is the max over ranks.  Other workloads (--workload): bf_8k_r15 (configs[3]; at N > 1 the image is cut into row
-strips with radius-deep halos, strong scaling), btf_4k (configs[2]), bf_lenna (configs[0] geometry), bf_1080p /
-abf_1080p / btf_1080p (configs[4] frames).
+Default workload: BASELINE.json configs[3] -- bilateral filter, radius 15 (ksize 31), on a synthetic 7680x4320 RGB image:
+the largest single-GPU configuration the metric is quoted on and the one the 8-GPU target is stated for.  A "step" is one
+pass of the filter over one frame.  N = 1: the whole frame on one B200.  N > 1 (torchrun, one process per GPU): the frame
+is cut into N row strips (STRONG scaling); a rank keeps only its OWN rows on its device and gets the radius-deep halo rows
+from the neighbouring ranks' device memory over NVLink inside the timed region -- either staged by the filter kernel
+itself straight from the neighbour's buffer (CUDA IPC pointers, --halo fused, the default for BF / ABF) or pulled by
+peer-to-peer row copies (--halo copy; always for BTF, whose strips carry nitr x 17 halo rows and recompute the
+overlap).  Outside the timed region the strips are gathered and compared with the single-GPU result, the reference's own
+CUDA kernel and oracle spot rows ("strip_parity").
 
-One JSON line on stdout.  `value` = whole-job Mpixel/s with inputs resident in HBM; `e2e` = the same through the
-public API with pinned HOST buffers, H2D + kernel + D2H inside the timed region, four frames in flight; `roofline` =
-the dominant kernel against the measured HBM peak (MEASURED_PEAKS.json) -- the stencil kernels are issue-bound, not
-HBM-bound, so `issue` gives the achieved taps/s and the estimated issue-slot utilisation next to it; `cpu_baseline`
-= the reference's own C++ CPU path (oracle/_ref/libvip_ref_cpu.so, compiled unmodified from the reference) on a
-bounded sample, on this box's host cores.
+One JSON line on stdout.  `value` = whole-job Mpixel/s with inputs resident in HBM; `e2e` = the same through the public
+API from pinned HOST buffers (every step uploads the rank's own rows, filters, downloads its rows; neighbours order
+themselves with device-side flags -- vip_link_*); `roofline` = the dominant kernel's ALGORITHMIC work (taps/s x the
+minimal per-tap instruction mix of SURVEY.md 8d) against the FP32 issue rate measured live on this GPU, with the HBM
+figures next to it; `ref_cuda` = the reference's own kernel recompiled for sm_100a on the same GPU (the kernel to beat);
+`cpu_baseline` = the reference's own C++ CPU path on a bounded sample; `per_workload` = the same figures for the other
+configured workloads (ABF 4K r=7, BTF 4K k=9 x3, the 1080p all-three-filters frame stream).
 
 --impl reference times the reference's CPU implementation of the same workload (bounded sample per step).
 """
@@ -32,34 +37,62 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 WORKLOADS = {
     # name: (filter, width, height, ksize, nitr, description)
-    "abf_4k_r7": ("abf", 3840, 2160, 15, 0, "adaptive bilateral filter radius=7 on synthetic 3840x2160 RGB (BASELINE configs[1])"),
+    "bf_8k_r15": ("bf", 7680, 4320, 31, 0, "bilateral filter radius=15 on synthetic 7680x4320 RGB, row strips + halos at N > 1 (BASELINE configs[3])"),
+    "abf_4k_r7": ("abf", 3840, 2160, 15, 0, "adaptive bilateral filter radius=7 on synthetic 3840x2160 RGB (configs[1])"),
     "btf_4k": ("btf", 3840, 2160, 9, 3, "bilateral texture filter k=9, 3 iterations on synthetic 3840x2160 RGB (configs[2])"),
-    "bf_8k_r15": ("bf", 7680, 4320, 31, 0, "bilateral filter radius=15 on synthetic 7680x4320 RGB, row strips + halos (configs[3])"),
     "bf_lenna": ("bf", 512, 512, 11, 0, "bilateral filter radius=5 on sample_image/lenna.png 512x512 BGR (configs[0]; committed fixture)"),
     "bf_4k_r5": ("bf", 3840, 2160, 11, 0, "bilateral filter radius=5 on synthetic 3840x2160 RGB"),
     "bf_1080p": ("bf", 1920, 1080, 9, 0, "bilateral filter k=9 on 1080p frames (configs[4])"),
     "abf_1080p": ("abf", 1920, 1080, 9, 0, "adaptive bilateral filter k=9 on 1080p frames (configs[4])"),
     "btf_1080p": ("btf", 1920, 1080, 9, 3, "bilateral texture filter k=9 nitr=3 on 1080p frames (configs[4])"),
-    "stream_1080p": ("all", 1920, 1080, 9, 3, "1080p RGB frame stream through all three filters (BF k=9, ABF k=9, BTF k=9 x3), frames dealt to the GPUs (configs[4]; --steps = frames per GPU)"),
+    "stream_1080p": ("all", 1920, 1080, 9, 3, "1080p RGB frame stream through all three filters (BF k=9, ABF k=9, BTF k=9 x3), frames dealt to the GPUs (configs[4]; a step = one frame per GPU)"),
 }
+DEFAULT_WORKLOAD = "bf_8k_r15"
+PER_WORKLOAD = ["abf_4k_r7", "btf_4k", "stream_1080p"]
 L2_BYTES = 126 * 1024 * 1024
+NS = 3   # frames in flight of the end-to-end legs
 
-# non-zero taps of the circular mask and the per-tap instruction estimates of DESIGN.md
+
 def mask_taps(r):
     return sum(1 for y in range(-r, r + 1) for x in range(-r, r + 1) if x * x + y * y <= r * r)
 
 
-def synth_frame(w, h, seed):
-    """S-rand: i.i.d. uniform bytes (content-independent, like the reference's test fixtures)."""
-    return np.random.RandomState(seed).randint(0, 256, size=(h, w, 3), dtype=np.uint8)
+# minimal thread-instructions per tap (SURVEY.md 8d "Roofline formulas"): LUT LDS, SAD, FMUL, 3 FFMA, FADD + the pixel LDS
+# and 3 I2F amortised over the P outputs a thread produces
+def i_min(kind, P):
+    return {"bf": 7 + 4.0 / P, "jbf": 7 + 5.0 / P, "abf": 15 + 4.0 / P}[kind]
 
 
+OUTPUTS_PER_THREAD = {"bf": 8, "jbf": 8, "abf": 4}   # csrc/stencil.cu outputs_per_thread()
+FLOP_PER_TAP = {"bf": 8, "jbf": 8, "abf": 16}
+
+
+# ---------------------------------------------------------------- synthetic content
 def lenna_frame():
     """configs[0]: sample_image/lenna.png decoded to BGR (committed fixture, tests/golden/make_golden_lenna.py)."""
     return np.ascontiguousarray(np.load(os.path.join(ROOT, "tests", "golden", "lenna_vectors.npz"))["lenna_bgr"])
+
+
+def synth_frame(w, h, seed, content="rand"):
+    """S-rand: i.i.d. uniform bytes (the headline: content-independent, like the reference's test fixtures);
+    S-narrow: uniform [100, 120) like the reference benchmark (sample/benchmark/main.cpp:210-213); S-nat: lenna, mirrored
+    tiling; smooth: the tests' synthetic natural-ish image."""
+    if content == "rand":
+        return np.random.RandomState(seed).randint(0, 256, size=(h, w, 3), dtype=np.uint8)
+    if content == "narrow":
+        return np.random.RandomState(seed).randint(100, 120, size=(h, w, 3), dtype=np.uint8)
+    if content == "nat":
+        t = lenna_frame()
+        t = np.roll(t, seed % 97, axis=1)
+        t = np.concatenate([np.concatenate([t, t[:, ::-1]], 1), np.concatenate([t[::-1], t[::-1, ::-1]], 1)], 0)
+        return np.ascontiguousarray(np.tile(t, (h // t.shape[0] + 1, w // t.shape[1] + 1, 1))[:h, :w])
+    import _oracle as O
+    t = O.smooth_image(min(w, 512), min(h, 432), seed=seed)
+    return np.ascontiguousarray(np.tile(t, (h // t.shape[0] + 1, w // t.shape[1] + 1, 1))[:h, :w])
 
 
 class ClockSampler:
@@ -72,7 +105,7 @@ class ClockSampler:
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50",
                                           "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -86,12 +119,12 @@ class ClockSampler:
     def mark(self):
         return len(self.rows)
 
-    def stop(self, first=0):
+    def stop(self, first=0, last=None):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.12)
         self.proc.terminate()
-        rows = self.rows[first:] or self.rows
+        rows = self.rows[first:last] or self.rows[first:] or self.rows
         sm, mx, reasons = [], [], set()
         for r in rows:
             try:
@@ -106,10 +139,11 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_reference(filt, w, h, ksize, nitr, sample_rows, threads, repeats=1):
-    """The reference's own CPU path on a full-width crop of `sample_rows` rows; returns (Mpixel/s, kind, cores, what)."""
+# ---------------------------------------------------------------- the reference's CPU path (baseline / reference arm)
+def cpu_reference(filt, w, h, ksize, nitr, sample_rows, threads, repeats=1, content="rand"):
+    """The reference's own CPU path on a full-width crop of `sample_rows` rows; returns (Mpixel/s, kind, cores, what, s)."""
     import _oracle as O
-    img = np.ascontiguousarray(lenna_frame()[:sample_rows]) if (w, h, filt) == (512, 512, "bf") else synth_frame(w, sample_rows, 42)
+    img = np.ascontiguousarray(lenna_frame()[:sample_rows]) if (w, h, filt) == (512, 512, "bf") else synth_frame(w, sample_rows, 42, content)
     dst = np.empty_like(img)
     if O.have_ref_cpu():
         R = O.ref_cpu()
@@ -119,7 +153,6 @@ def cpu_reference(filt, w, h, ksize, nitr, sample_rows, threads, repeats=1):
         r_bf = lambda: R.ref_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0)
         r_abf = lambda: R.ref_adaptive_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0)
         r_btf = lambda: R.ref_bilateral_texture_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, nitr)
-        run = {"bf": r_bf, "abf": r_abf, "btf": r_btf, "all": lambda: (r_bf(), r_abf(), r_btf())}[filt]
     else:
         kind = "port"
         L = O.oracle()
@@ -128,7 +161,7 @@ def cpu_reference(filt, w, h, ksize, nitr, sample_rows, threads, repeats=1):
         r_bf = lambda: L.vipo_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0, 1)
         r_abf = lambda: L.vipo_adaptive_bilateral_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, 10.0, 30.0, 1)
         r_btf = lambda: L.vipo_bilateral_texture_filter(img.ctypes.data, dst.ctypes.data, w, sample_rows, ksize, nitr, 1)
-        run = {"bf": r_bf, "abf": r_abf, "btf": r_btf, "all": lambda: (r_bf(), r_abf(), r_btf())}[filt]
+    run = {"bf": r_bf, "abf": r_abf, "btf": r_btf, "all": lambda: (r_bf(), r_abf(), r_btf())}[filt]
     best = float("inf")
     for _ in range(repeats):
         t0 = time.perf_counter()
@@ -139,38 +172,38 @@ def cpu_reference(filt, w, h, ksize, nitr, sample_rows, threads, repeats=1):
     return mpix, kind, cores, what, best
 
 
-def sample_rows_for(filt, w, h, ksize):
+def sample_rows_for(filt, w, h, ksize, budget_taps=1e9):
     taps = ksize * ksize * {"bf": 1, "abf": 2, "btf": 4, "all": 7}[filt]
-    # ~1e9 tap evaluations per sample: about a second on a many-core host, bounded on a small one
-    rows = int(1e9 / (taps * w))
+    rows = int(budget_taps / (taps * w))
     return max(4 * ksize, min(h, rows - rows % 8))
 
 
 def run_reference_arm(args, wl):
     filt, w, h, ksize, nitr, desc = wl
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
+    if int(os.environ.get("RANK", "0")) != 0:
         return
     rows = sample_rows_for(filt, w, h, ksize)
     # calibrate once so that warmup + steps stay within ~2 minutes whatever the host is
-    _, _, _, _, t_cal = cpu_reference(filt, w, h, ksize, nitr, rows, args.cpu_threads)
+    _, _, _, _, t_cal = cpu_reference(filt, w, h, ksize, nitr, rows, args.cpu_threads, content=args.content)
     budget_s = 120.0 / max(1, args.warmup + args.steps)
     if t_cal > budget_s:
         rows = max(4 * ksize, int(rows * budget_s / t_cal) // 4 * 4)
     times = []
     cores = kind = what = None
     for i in range(args.warmup + args.steps):
-        mp, kind, cores, what, t = cpu_reference(filt, w, h, ksize, nitr, rows, args.cpu_threads)
+        mp, kind, cores, what, t = cpu_reference(filt, w, h, ksize, nitr, rows, args.cpu_threads, content=args.content)
         if i >= args.warmup:
             times.append(t)
     ms = 1e3 * float(np.mean(times))
     value = w * rows / (ms * 1e-3) / 1e6
     out = {
         "impl": "reference", "metric": f"{filt}_throughput", "value": value, "unit": "Mpixel/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "strong" if args.gpus > 1 and filt != "all" else "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "lenna.png" if args.workload == "bf_lenna" else "synthetic",
         "config": {"workload": args.workload, "description": desc, "width": w, "height": h, "ksize": ksize, "nitr": nitr,
-                   "sample": f"each step filters a {w}x{rows} full-width crop (bounded sample of the workload frame)"},
+                   "content": args.content,
+                   "sample": f"each step filters a {w}x{rows} full-width crop (bounded sample of the workload frame); Mpixel/s normalises"},
         "cpu_baseline": {"value": value, "unit": "Mpixel/s", "cores": cores, "kind": kind, "sample": what},
         "e2e": {"value": value, "unit": "Mpixel/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -178,196 +211,464 @@ def run_reference_arm(args, wl):
     print(json.dumps(out), flush=True)
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="abf_4k_r7", choices=sorted(WORKLOADS))
-    ap.add_argument("--cpu-threads", type=int, default=0, help="threads of the CPU baseline (0 = all host cores)")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-probe", action="store_true", help="skip the issue-rate probe kernels (for ncu launch lists)")
-    ap.add_argument("--content", default="rand", choices=["rand", "smooth"], help="synthetic content")
-    args = ap.parse_args()
-    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
-    wl = WORKLOADS[args.workload]
-    if args.impl == "reference":
-        run_reference_arm(args, wl)
-        return
+# ---------------------------------------------------------------- host placement
+def bind_to_gpu_numa_node(index):
+    """Pin this process (and therefore the pages cudaHostAlloc first-touches) to the NUMA node / CPUs the GPU hangs off.
+    Returns what was done, for the JSON line."""
+    info = {"numa_node": None, "cpus": None}
+    try:
+        bus = subprocess.run(["nvidia-smi", "--query-gpu=pci.bus_id", "--format=csv,noheader", "-i", str(index)],
+                             capture_output=True, text=True, timeout=10).stdout.strip().lower()
+        if bus.startswith("00000000:"):
+            bus = bus[4:]
+        base = f"/sys/bus/pci/devices/{bus}"
+        node = int(open(f"{base}/numa_node").read().strip())
+        cpus = open(f"{base}/local_cpulist").read().strip()
+        info["numa_node"], info["cpus"] = node, cpus
+        if cpus:
+            ids = set()
+            for part in cpus.split(","):
+                a, _, b = part.partition("-")
+                ids.update(range(int(a), int(b or a) + 1))
+            ids &= os.sched_getaffinity(0)
+            if ids:
+                os.sched_setaffinity(0, ids)
+                info["bound"] = True
+    except Exception as exc:  # placement is an optimisation, never a reason to fail
+        info["error"] = str(exc)[:80]
+    return info
 
-    import torch
-    import torch.distributed as dist
+
+# ---------------------------------------------------------------- jobs
+class Ctx:
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.args = torch, dist, args
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for the CPU baseline)")
+        # fewer GPUs than ranks (the 1-GPU test box running the 2-rank strip test): ranks share devices and the plumbing
+        # falls back to gloo (NCCL refuses two ranks on one device); the data path -- CUDA IPC + flags -- is the same
+        self.shared_gpu = torch.cuda.device_count() < min(self.world, int(os.environ.get("LOCAL_WORLD_SIZE", self.world)))
+        self.device_index = self.local_rank % torch.cuda.device_count()
+        torch.cuda.set_device(self.device_index)
+        self.placement = bind_to_gpu_numa_node(self.device_index)
+        if self.world > 1:
+            if self.shared_gpu:
+                dist.init_process_group("gloo")
+            else:
+                dist.init_process_group("nccl", device_id=torch.device("cuda", self.device_index))
+        self.sm_count = torch.cuda.get_device_properties(self.device_index).multi_processor_count
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, x):
+        if self.world == 1:
+            return float(x)
+        t = self.torch.tensor([float(x)], device="cpu" if self.shared_gpu else "cuda", dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def all_gather_object(self, obj):
+        if self.world == 1:
+            return [obj]
+        out = [None] * self.world
+        self.dist.all_gather_object(out, obj)
+        return out
+
+
+def timed_steps(ctx, step, steps, warmup, sampler=None):
+    """W untimed + K timed steps, bracketed by barrier + synchronize, CUDA events on the launching stream, max over ranks.
+    Returns (ms per step, launches, (clock mark before, after))."""
     import various_image_processings_b200 as vip
-
-    filt, w, h, ksize, nitr, desc = wl
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for the CPU baseline)")
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    radius = ksize // 2
-
-    # ---- work decomposition
-    strong = (filt == "bf" and args.workload == "bf_8k_r15" and world > 1)
-    if strong:
-        plan = vip.plan_strips(h, world, vip.halo_rows("bf", ksize))[rank]
-        y0, y1, s0, s1 = plan
-        strip = vip.to_strip(plan)
-    else:
-        y0, y1, s0, s1 = 0, h, 0, h
-        strip = None
-    out_rows = y1 - y0
-    frame_bytes = w * h * 3
-    # inputs resident in HBM; rotate over enough distinct frames that in+out exceed the L2
-    n_pool = max(2, int(np.ceil(1.2 * L2_BYTES / (2.0 * w * (s1 - s0) * 3))))
-    n_pool = min(n_pool, 16)
-    if args.workload == "bf_lenna":
-        frames = [lenna_frame()] * n_pool
-    elif args.content == "rand":
-        frames = [synth_frame(w, h, 42 + 1000 * rank + i) for i in range(n_pool)]
-    else:
-        import _oracle as O
-        frames = [O.smooth_image(w, h, seed=42 + 1000 * rank + i) for i in range(n_pool)]
-    d_src = [torch.from_numpy(np.ascontiguousarray(f[s0:s1])).cuda() for f in frames]
-    d_dst = [torch.empty((out_rows, w, 3), dtype=torch.uint8, device="cuda") for _ in range(n_pool)]
-
-    if filt == "bf":
-        F = vip.CudaBilateralFilter(w, h, ksize)
-        if strong:
-            step = lambda i: F.bilateral_filter_strip(d_src[i % n_pool], d_dst[i % n_pool], strip)
-        else:
-            step = lambda i: F.bilateral_filter_async(d_src[i % n_pool], d_dst[i % n_pool])
-    elif filt == "abf":
-        F = vip.CudaAdaptiveBilateralFilter(w, h, ksize)
-        step = lambda i: F.execute_async(d_src[i % n_pool], d_dst[i % n_pool])
-    elif filt == "btf":
-        F = vip.CudaBilateralTextureFilter(w, h, ksize, nitr)
-        step = lambda i: F.execute_async(d_src[i % n_pool], d_dst[i % n_pool])
-    else:
-        F = (vip.CudaBilateralFilter(w, h, ksize), vip.CudaAdaptiveBilateralFilter(w, h, ksize),
-             vip.CudaBilateralTextureFilter(w, h, ksize, nitr))
-        d_dst2 = [torch.empty_like(d) for d in d_dst]
-        d_dst3 = [torch.empty_like(d) for d in d_dst]
-
-        def step(i):
-            j = i % n_pool
-            F[0].bilateral_filter_async(d_src[j], d_dst[j])
-            F[1].execute_async(d_src[j], d_dst2[j])
-            F[2].execute_async(d_src[j], d_dst3[j])
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    for i in range(args.warmup):
+    torch = ctx.torch
+    for i in range(warmup):
         step(i)
-    barrier()
-    mark = sampler.mark()
+    ctx.barrier()
+    m0 = sampler.mark() if sampler else 0
     n0 = vip.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
-    for i in range(args.steps):
-        step(i)
+    for i in range(steps):
+        step(warmup + i)
     ev1.record()
-    barrier()
+    ctx.barrier()
+    m1 = sampler.mark() if sampler else 0
     launches = vip.launch_count() - n0
-    ms_total = ev0.elapsed_time(ev1)
-    clocks = sampler.stop(mark)
-    if world > 1:
-        t = torch.tensor([ms_total], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total = float(t.item())
-    ms_step = ms_total / args.steps
-    pixels_step = (w * h) if strong else (w * h * world)   # strong: one image over all ranks; weak: one frame per rank
-    value = pixels_step / (ms_step * 1e-3) / 1e6
+    return ctx.max_over_ranks(ev0.elapsed_time(ev1)) / steps, launches, (m0, m1)
 
-    # ---- end to end through the public API with pinned host buffers, two frames in flight
-    e2e_steps = max(8, min(args.steps, 40))
-    slots = []
-    NS = 4   # frames in flight: upload, filter and download of different frames overlap on NS streams
-    for s in range(NS):
-        src_img, dst_img = vip.DeviceImage(w, s1 - s0, 3), vip.DeviceImage(w, out_rows, 3)
-        hin, hout = vip.PinnedBuffer(w * (s1 - s0) * 3), vip.PinnedBuffer(w * out_rows * 3)
-        hin.array[:] = frames[s % n_pool][s0:s1].reshape(-1)
-        slots.append((src_img, dst_img, hin, hout, torch.cuda.Stream()))
-    if filt == "btf":
-        F2 = [F] + [vip.CudaBilateralTextureFilter(w, h, ksize, nitr) for _ in range(NS - 1)]   # scratch is per object
-    n_out = 3 if filt == "all" else 1                                 # result images downloaded per step
-    if filt == "all":
-        F2 = [F[2]] + [vip.CudaBilateralTextureFilter(w, h, ksize, nitr) for _ in range(NS - 1)]
-        extra = [[(vip.DeviceImage(w, out_rows, 3), vip.PinnedBuffer(w * out_rows * 3)) for _ in range(2)] for _ in range(NS)]
 
-    def e2e_step(i):
-        src_img, dst_img, hin, hout, st = slots[i % NS]
-        src_img.upload(hin.array, stream=st)
-        if filt == "bf":
-            if strong:
-                F.bilateral_filter_strip(src_img, dst_img, strip, stream=st)
-            else:
-                F.bilateral_filter_async(src_img, dst_img, stream=st)
-        elif filt == "abf":
-            F.execute_async(src_img, dst_img, stream=st)
-        elif filt == "btf":
-            F2[i % NS].execute_async(src_img, dst_img, stream=st)
+class Job:
+    """One workload on this rank: buffers, the device-resident step, the end-to-end step, parity of the split."""
+
+    def __init__(self, ctx, name, halo_mode):
+        import various_image_processings_b200 as vip
+        self.vip, self.ctx, self.name = vip, ctx, name
+        self.filt, self.w, self.h, self.ksize, self.nitr, self.desc = WORKLOADS[name]
+        torch = ctx.torch
+        world, rank = ctx.world, ctx.rank
+        content = ctx.args.content
+        w, h, ksize, nitr, filt = self.w, self.h, self.ksize, self.nitr, self.filt
+        self.rb = w * 3
+        # ---- decomposition: strips of one frame (strong) when the filter and the frame allow it, else a frame per rank
+        self.halo = 0 if filt == "all" else vip.halo_rows(filt, ksize, nitr, exchange_between_iterations=False)
+        self.strong = world > 1 and filt != "all" and h // world >= max(self.halo, 32)
+        if self.strong:
+            plans = vip.plan_strips(h, world, self.halo)
+            self.plans = plans
+            self.y0, self.y1, self.s0, self.s1 = plans[rank]
         else:
-            (d2, h2), (d3, h3) = extra[i % NS]
-            F[0].bilateral_filter_async(src_img, dst_img, stream=st)
-            F[1].execute_async(src_img, d2, stream=st)
-            F2[i % NS].execute_async(src_img, d3, stream=st)
-            d2.download(h2.array, stream=st)
-            d3.download(h3.array, stream=st)
-        dst_img.download(hout.array, stream=st)
+            self.plans = None
+            self.y0, self.y1, self.s0, self.s1 = 0, h, 0, h
+        self.own = self.y1 - self.y0
+        self.halo_mode = "none" if not self.strong else ("copy" if filt == "btf" else halo_mode)
+        self.has_above = self.strong and rank > 0
+        self.has_below = self.strong and rank < world - 1
+        # ---- frames: rotate over enough distinct resident frames that in + out exceed the L2
+        n_pool = max(2, int(np.ceil(1.2 * L2_BYTES / (2.0 * self.rb * self.own))))
+        self.n_pool = n_pool = min(n_pool, 12)
+        seed0 = 42 if self.strong else 42 + 1000 * rank      # strips: every rank cuts the SAME frames
+        self.frame0 = None
+        self.host_own = []
+        for i in range(n_pool):
+            f = lenna_frame() if name == "bf_lenna" else synth_frame(w, h, seed0 + i, content)
+            if i == 0:
+                self.frame0 = f
+            self.host_own.append(np.ascontiguousarray(f[self.y0:self.y1]))
+        # ---- filters
+        if filt == "bf":
+            self.F = vip.CudaBilateralFilter(w, h, ksize)
+        elif filt == "abf":
+            self.F = vip.CudaAdaptiveBilateralFilter(w, h, ksize)
+        elif filt == "btf":
+            self.F = vip.CudaBilateralTextureFilter(w, h, ksize, nitr)
+        else:
+            self.F = (vip.CudaBilateralFilter(w, h, ksize), vip.CudaAdaptiveBilateralFilter(w, h, ksize),
+                      vip.CudaBilateralTextureFilter(w, h, ksize, nitr))
+        self.n_out = 3 if filt == "all" else 1
+        # ---- device buffers: source strips hold [s0, s1) (own rows uploaded, halo rows only ever written by the halo
+        #      pull), destinations the own rows.  DeviceImage = one cudaMalloc each, so the base pointer can be exported.
+        srows = self.s1 - self.s0
+        self.src = [vip.DeviceImage(w, srows, 3) for _ in range(n_pool)]
+        self.dst = [[vip.DeviceImage(w, self.own, 3) for _ in range(self.n_out)] for _ in range(n_pool)]
+        for j in range(n_pool):
+            self.src[j].upload_rows(self.host_own[j], self.y0 - self.s0, self.own, stream=0)
+        if filt == "btf" and self.strong:
+            self.pp = [vip.DeviceImage(w, srows, 3), vip.DeviceImage(w, srows, 3)]
+        # ---- end-to-end slots
+        self.slots = []
+        for s in range(NS):
+            sl = {"src": vip.DeviceImage(w, srows, 3), "dst": [vip.DeviceImage(w, self.own, 3) for _ in range(self.n_out)],
+                  "hin": vip.PinnedBuffer(self.rb * self.own), "hout": [vip.PinnedBuffer(self.rb * self.own) for _ in range(self.n_out)],
+                  "stream": torch.cuda.Stream()}
+            sl["hin"].array[:] = self.host_own[s % n_pool].reshape(-1)
+            if filt in ("btf", "all"):   # BTF scratch is per object: one object per frame in flight
+                sl["btf"] = vip.CudaBilateralTextureFilter(w, h, ksize, nitr)
+                if self.strong:
+                    sl["pp"] = [vip.DeviceImage(w, srows, 3), vip.DeviceImage(w, srows, 3)]
+            self.slots.append(sl)
+        # ---- neighbours: IPC handles of every source buffer + one flag block per rank
+        self.link = None
+        self.transport = "none"
+        self.e2e_i = 0                      # running step counter of the end-to-end legs (same on every rank)
+        self.prev_step = [0] * NS           # last step number that used each slot
+        self.nbr = {}
+        if self.strong:
+            self.link = vip.StripLink(NS)
+            mine = {"src": [vip.ipc_export(b) for b in self.src], "slot": [vip.ipc_export(sl["src"]) for sl in self.slots],
+                    "link": self.link.export(), "plan": tuple(plans[rank]), "device": ctx.device_index}
+            every = ctx.all_gather_object(mine)
+            for side, r in (("above", rank - 1), ("below", rank + 1)):
+                if 0 <= r < world:
+                    o = every[r]
+                    self.nbr[side] = {"src": [vip.ipc_open(hd) for hd in o["src"]], "slot": [vip.ipc_open(hd) for hd in o["slot"]],
+                                      "plan": o["plan"]}
+            self.link.connect(every[rank - 1]["link"] if rank > 0 else None, every[rank + 1]["link"] if rank < world - 1 else None)
+            self.transport = "cuda-ipc peer pointers over NVLink (%s)" % (
+                "halo rows staged by the filter kernel straight from the neighbours' buffers" if self.halo_mode == "fused"
+                else "cudaMemcpyAsync peer copies of the halo rows")
+        ctx.barrier()
 
-    for i in range(NS):
-        e2e_step(i)
-    barrier()
-    t0 = time.perf_counter()
-    for i in range(e2e_steps):
-        e2e_step(i)
-    for sl in slots:
-        sl[4].synchronize()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    e2e_value = pixels_step * e2e_steps / e2e_s / 1e6
+    # strip descriptors ---------------------------------------------------------------------------------------------
+    def _peer_halo(self, which, j):
+        """struct vip_halo over the neighbours' OWN rows of pool frame / slot j."""
+        vip = self.vip
 
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+        def side(name):
+            if name not in self.nbr:
+                return None
+            ny0, ny1, ns0, _ = self.nbr[name]["plan"]
+            return (self.nbr[name][which][j] + (ny0 - ns0) * self.rb, ny0, ny1 - ny0)
+        return vip.make_halo(above=side("above"), below=side("below"))
 
-    # ---- roofline of the dominant kernel
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except (OSError, ValueError):
-        pass
-    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
-    local_pixels = w * out_rows
-    kernels_per_step = launches / max(args.steps, 1)
-    taps = mask_taps(radius if filt not in ("btf", "all") else ksize - 1)
+    def _pull_halo(self, which, j, dst_img, stream):
+        """explicit halo pull: rows [s0, y0) from the rank above and [y1, s1) from the rank below, peer-to-peer"""
+        vip = self.vip
+        if "above" in self.nbr and self.y0 > self.s0:
+            ny0, ny1, ns0, _ = self.nbr["above"]["plan"]
+            vip.copy_rows(dst_img, self.s0, self.nbr["above"][which][j], ns0, self.s0, self.y0 - self.s0, self.w, stream=stream)
+        if "below" in self.nbr and self.s1 > self.y1:
+            ny0, ny1, ns0, _ = self.nbr["below"]["plan"]
+            vip.copy_rows(dst_img, self.s0, self.nbr["below"][which][j], ns0, self.y1, self.s1 - self.y1, self.w, stream=stream)
+
+    def _filter(self, which, j, src_img, dst_imgs, stream, btf=None, pp=None):
+        """the filter pass of one step on this rank's rows; returns the (image, first row) holding the result"""
+        vip, filt = self.vip, self.filt
+        if not self.strong:
+            if filt == "bf":
+                self.F.bilateral_filter_async(src_img, dst_imgs[0], stream=stream)
+            elif filt == "abf":
+                self.F.execute_async(src_img, dst_imgs[0], stream=stream)
+            elif filt == "btf":
+                (btf or self.F).execute_async(src_img, dst_imgs[0], stream=stream)
+            else:
+                self.F[0].bilateral_filter_async(src_img, dst_imgs[0], stream=stream)
+                self.F[1].execute_async(src_img, dst_imgs[1], stream=stream)
+                (btf or self.F[2]).execute_async(src_img, dst_imgs[2], stream=stream)
+            return
+        if self.halo_mode == "fused":
+            own_ptr = src_img.row_ptr(self.y0 - self.s0)
+            st = vip.Strip(self.y0, self.own, self.y0, self.y0, self.own)
+            halo = self._peer_halo(which, j)
+            if filt == "bf":
+                self.F.bilateral_filter_strip_peer(own_ptr, halo, dst_imgs[0], st, stream=stream)
+            else:
+                self.F.execute_strip_peer(own_ptr, halo, dst_imgs[0], st, stream=stream)
+            return
+        self._pull_halo(which, j, src_img, stream)
+        if filt in ("bf", "abf"):
+            st = vip.Strip(self.s0, self.s1 - self.s0, self.y0, self.y0, self.own)
+            if filt == "bf":
+                self.F.bilateral_filter_strip(src_img, dst_imgs[0], st, stream=stream)
+            else:
+                self.F.execute_strip(src_img, dst_imgs[0], st, stream=stream)
+            return
+        # BTF strip, deep halo: iteration `it` also produces the rows the remaining iterations will read around the own rows
+        B = btf or self.F
+        per_it = self.halo // max(1, self.nitr)
+        cur = src_img
+        for it in range(self.nitr):
+            margin = (self.nitr - 1 - it) * per_it
+            oy0, oy1 = max(0, self.y0 - margin), min(self.h, self.y1 + margin)
+            last = it == self.nitr - 1
+            out = dst_imgs[0] if last else pp[it & 1]
+            st = vip.Strip(self.s0, self.s1 - self.s0, self.y0 if last else self.s0, oy0, oy1 - oy0)
+            B.iterate_strip(cur, out, st, stream=stream)
+            cur = out
+
+    # the two legs ---------------------------------------------------------------------------------------------------
+    def step(self, i):
+        j = i % self.n_pool
+        self._filter("src", j, self.src[j], self.dst[j], None, pp=getattr(self, "pp", None))
+
+    def e2e_step(self, i):
+        """step i (from 0): upload own rows -> (neighbours ready) -> filter -> (tell neighbours) -> download"""
+        s = i % NS
+        sl = self.slots[s]
+        st = sl["stream"]
+        step_no = i + 1
+        if self.link is not None and self.prev_step[s]:
+            self.link.wait_consumed(s, self.prev_step[s], stream=st)   # neighbours are done with the rows this upload overwrites
+        self.prev_step[s] = step_no
+        sl["src"].upload_rows(sl["hin"].array.reshape(self.own, self.w, 3), self.y0 - self.s0, self.own, stream=st)
+        if self.link is not None:
+            self.link.signal_ready(s, step_no, stream=st)
+            self.link.wait_ready(s, step_no, stream=st)
+        self._filter("slot", s, sl["src"], sl["dst"], st, btf=sl.get("btf"), pp=sl.get("pp"))
+        if self.link is not None:
+            self.link.signal_consumed(s, step_no, stream=st)
+        for d, hb in zip(sl["dst"], sl["hout"]):
+            d.download_rows(hb.array.reshape(self.own, self.w, 3), 0, self.own, stream=st)
+
+    def run_e2e(self, steps):
+        """returns seconds per step (max over ranks) of the pipelined end-to-end leg"""
+        ctx = self.ctx
+        base = self.e2e_i
+        for i in range(NS):
+            self.e2e_step(base + i)
+        for sl in self.slots:
+            sl["stream"].synchronize()
+        ctx.barrier()
+        t0 = time.perf_counter()
+        for i in range(NS, NS + steps):
+            self.e2e_step(base + i)
+        for sl in self.slots:
+            sl["stream"].synchronize()
+        dt = time.perf_counter() - t0
+        self.e2e_i = base + NS + steps
+        if self.link is not None:
+            self.link.status()
+        return ctx.max_over_ranks(dt) / steps
+
+    def run_copy_ceiling(self, steps):
+        """the same host<->device traffic with no kernels: what the box's host side allows at this N"""
+        ctx = self.ctx
+
+        def one(i):
+            sl = self.slots[i % NS]
+            st = sl["stream"]
+            sl["src"].upload_rows(sl["hin"].array.reshape(self.own, self.w, 3), self.y0 - self.s0, self.own, stream=st)
+            for d, hb in zip(sl["dst"], sl["hout"]):
+                d.download_rows(hb.array.reshape(self.own, self.w, 3), 0, self.own, stream=st)
+        for i in range(NS):
+            one(i)
+        for sl in self.slots:
+            sl["stream"].synchronize()
+        ctx.barrier()
+        t0 = time.perf_counter()
+        for i in range(steps):
+            one(i)
+        for sl in self.slots:
+            sl["stream"].synchronize()
+        return ctx.max_over_ranks(time.perf_counter() - t0) / steps
+
+    def close(self):
+        """unmap the neighbours' buffers before anybody frees them"""
+        self.ctx.barrier()
+        for side in self.nbr.values():
+            for p in side["src"] + side["slot"]:
+                self.vip.ipc_close(p)
+        self.nbr = {}
+        self.link = None
+        self.ctx.barrier()
+
+    # parity of the split --------------------------------------------------------------------------------------------
+    def check_parity(self):
+        """Outside the timed region: frame 0 through the strip path (device-resident AND end-to-end), gathered on rank 0
+        and compared with (a) the whole frame filtered on one GPU, (b) the reference's own CUDA kernel on that GPU,
+        (c) oracle rows at the strip boundaries.  Returns a dict for the JSON line (rank 0) or None."""
+        import _oracle as O
+        ctx, vip, torch = self.ctx, self.vip, self.ctx.torch
+        w, h, filt = self.w, self.h, self.filt
+        if filt == "all":
+            return None
+        self.step(0)                          # pool frame 0 -> dst[0]
+        torch.cuda.synchronize()
+        mine = self.dst[0][0].download()
+        self.ctx.barrier()
+        # the e2e path's result for slot 0 (holds pool frame 0 as input)
+        self.e2e_i = (self.e2e_i + NS - 1) // NS * NS      # next step that lands on slot 0
+        self.e2e_step(self.e2e_i)
+        self.e2e_i += 1
+        for sl in self.slots:
+            sl["stream"].synchronize()
+        if self.link is not None:
+            self.link.status()
+        mine_e2e = self.slots[0]["hout"][0].array.reshape(self.own, w, 3).copy()
+        if ctx.world > 1:
+            parts = [None] * ctx.world if ctx.rank == 0 else None
+            ctx.dist.gather_object((mine, mine_e2e), parts, dst=0)
+        else:
+            parts = [(mine, mine_e2e)]
+        if ctx.rank != 0:
+            return None
+        got = np.concatenate([p[0] for p in parts], 0)
+        got_e2e = np.concatenate([p[1] for p in parts], 0)
+        res = {"n_strips": ctx.world if self.strong else 1, "frame": "pool frame 0"}
+        d_src = torch.from_numpy(self.frame0).cuda()
+        d_one = torch.empty_like(d_src)
+        if self.strong:
+            if filt == "bf":
+                self.F.bilateral_filter_async(d_src, d_one)
+            elif filt == "abf":
+                self.F.execute_async(d_src, d_one)
+            else:
+                self.F.execute_async(d_src, d_one)
+            torch.cuda.synchronize()
+            one = d_one.cpu().numpy()
+            res["vs_single_gpu"] = "exact" if np.array_equal(got, one) else "DIFF(%d px)" % int((got != one).any(-1).sum())
+        res["e2e_vs_resident"] = "exact" if np.array_equal(got, got_e2e) else "DIFF(%d px)" % int((got != got_e2e).any(-1).sum())
+        # reference CUDA kernel on the same GPU: the parity oracle O2 and the kernel to beat
+        ref_cuda = None
+        if O.have_ref_cuda():
+            R = O.ref_cuda()
+            d_ref = torch.empty_like(d_src)
+            if filt == "bf":
+                p = R.refcu_bf_create(w, h, self.ksize, 10.0, 30.0)
+                run = lambda: R.refcu_bf_run(p, d_src.data_ptr(), d_ref.data_ptr())
+            elif filt == "abf":
+                p = R.refcu_abf_create(w, h, self.ksize, 10.0, 30.0)
+                run = lambda: R.refcu_abf_run(p, d_src.data_ptr(), d_ref.data_ptr())
+            else:
+                p = R.refcu_btf_create(w, h, self.ksize, self.nitr)
+                run = lambda: R.refcu_btf_run(p, d_src.data_ptr(), d_ref.data_ptr())
+            run()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(3):
+                run()               # the reference's public calls end with cudaDeviceSynchronize (src/*_impl.cu)
+            e1.record()
+            torch.cuda.synchronize()
+            ref_ms = e0.elapsed_time(e1) / 3
+            ref = d_ref.cpu().numpy()
+            same = np.array_equal(got, ref)
+            res["vs_ref_cuda"] = "exact" if same else "DIFF(%d px, max %d)" % (int((got != ref).any(-1).sum()), int(np.abs(got.astype(int) - ref.astype(int)).max()))
+            ref_cuda = {"ms": ref_ms, "exact": bool(same), "what": "the reference's own kernel(s) (src/*_impl.cu compiled unmodified for sm_100a, oracle/_ref/libvip_ref_cuda.so), whole frame on this GPU, outside the timed region"}
+        # oracle rows at the strip boundaries (bounded CPU work)
+        if filt in ("bf", "abf"):
+            ys = sorted({0, h - 1} | ({pl.y0 for pl in self.plans[1:]} | {pl.y0 - 1 for pl in self.plans[1:]} if self.strong else {h // 2}))
+            ys = ys[:6]
+            bad = 0
+            for y in ys:
+                want = O.o_rows("abf" if filt == "abf" else "bf", self.frame0, y, 1, self.ksize)
+                bad += int((want[0] != got[y]).any(-1).sum())
+            res["vs_oracle_rows"] = {"rows": ys, "mismatching_pixels": bad}
+        ok = all(v == "exact" for k, v in res.items() if k.startswith("vs_") and isinstance(v, str)) and \
+            res["e2e_vs_resident"] == "exact" and res.get("vs_oracle_rows", {}).get("mismatching_pixels", 0) == 0
+        res["verdict"] = "exact" if ok else "MISMATCH"
+        return res, ref_cuda
+
+
+def measure_job(ctx, name, steps, warmup, halo_mode, sampler=None, with_cpu=True, cpu_budget=1e9):
+    """All figures of one workload; rank 0 gets the dict, the others None."""
+    import various_image_processings_b200 as vip
+    torch = ctx.torch
+    job = Job(ctx, name, halo_mode)
+    filt, w, h, ksize, nitr = job.filt, job.w, job.h, job.ksize, job.nitr
+    ms_step, launches, marks = timed_steps(ctx, job.step, steps, warmup, sampler)
+    pixels_step = w * h if job.strong else w * h * ctx.world
+    value = pixels_step / (ms_step * 1e-3) / 1e6
+    e2e_steps = max(8, min(steps, 40))
+    e2e_s = job.run_e2e(e2e_steps)
+    e2e_value = pixels_step / e2e_s / 1e6
+    mark_end = sampler.mark() if sampler else 0
+    ceil_s = job.run_copy_ceiling(e2e_steps)
+    par = job.check_parity()
+    job.close()
+    if ctx.rank != 0:
+        return None, job
+    parity, ref_cuda = par if par else (None, None)
+
+    # ---- the dominant kernel, timed alone where a step is several kernels (BTF: the joint bilateral, 2k-1 window,
+    #      sigma_space k-1, sigma_color sqrt 3 -- src/bilateral_texture_filter_impl.cu:188), CUDA events, same frames
+    local_rows = job.own
     if filt in ("btf", "all"):
-        alg_bytes = local_pixels * 9.0                    # dominant kernel = joint bilateral: src + guide in, dst out
-        # several kernels per step: the dominant one (BTF's joint bilateral: ksize 2k-1, sigma_space k-1, sigma_color
-        # sqrt 3, src/bilateral_texture_filter_impl.cu:188) is timed alone, live, on the same resident frames (the
-        # filtered frame of the timed region serves as the guide), CUDA events on the launching stream
+        kind = "jbf"
+        radius = ksize - 1
         J = vip.CudaBilateralFilter(w, h, 2 * ksize - 1, float(ksize - 1), 3.0 ** 0.5)
-        d_tmp = torch.empty_like(d_dst[0])
-        jstep = lambda i: J.joint_bilateral_filter_async(d_src[i % n_pool], d_dst[i % n_pool], d_tmp)
+        srcs = [torch.from_numpy(job.host_own[j]).cuda() for j in range(job.n_pool)] if not job.strong else None
+        if job.strong:
+            # strip of the same height as this rank's rows, cut from a resident frame (kernel time of a strip)
+            full = torch.from_numpy(job.frame0).cuda()
+            g = torch.flip(full, dims=[0]).contiguous()
+            d_tmp = torch.empty((job.own, w, 3), dtype=torch.uint8, device="cuda")
+            stp = vip.Strip(0, h, job.y0, job.y0, job.own)
+            jstep = lambda i: J.joint_bilateral_filter_strip(full, g, d_tmp, stp)
+        else:
+            guides = [torch.flip(s, dims=[0]).contiguous() for s in srcs]
+            d_tmp = torch.empty_like(srcs[0])
+            jstep = lambda i: J.joint_bilateral_filter_async(srcs[i % job.n_pool], guides[i % job.n_pool], d_tmp)
         for i in range(3):
             jstep(i)
         torch.cuda.synchronize()
-        jn = max(10, min(args.steps, 50))
+        jn = max(10, min(steps, 50))
         j0, j1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         j0.record()
         for i in range(jn):
@@ -375,80 +676,156 @@ def main():
         j1.record()
         torch.cuda.synchronize()
         kernel_ms = j0.elapsed_time(j1) / jn
-        instr_per_tap = 8.5                               # JBF 17x17: smsp__inst_executed x 32 / taps (ncu, profiles/r01d)
-        packed_per_tap = 2.0
-        taps_per_px = taps * nitr + (2 * mask_taps(radius) if filt == "all" else 0)
+        launches_of_kernel_per_step = nitr
+        alg_bytes = w * local_rows * 9.0
     else:
-        alg_bytes = local_pixels * 6.0                    # 3 B in + 3 B out per pixel
+        kind = filt
+        radius = ksize // 2
         kernel_ms = ms_step
-        instr_per_tap = 18.1 if filt == "abf" else 7.8   # whole-kernel SASS instructions per tap measured by ncu (profiles/r01d; tile staging, box sums and epilogue included)
-        packed_per_tap = 4.2 if filt == "abf" else 2.0   # fp32x2 instructions among them (SASS of the tap loop): ABF 6 FADD2 + 4 FFMA2 per tap PAIR less the scalar edge taps; BF/JBF 1 FFMA2 {s0,s1} + 2 per pair {s2},{sk}
-        taps_per_px = taps
-    traffic = None
+        launches_of_kernel_per_step = 1
+        alg_bytes = w * local_rows * 6.0
+    taps = mask_taps(radius)
+    P = OUTPUTS_PER_THREAD[kind]
+    imin = i_min(kind, P)
+    taps_s = w * local_rows * taps / (kernel_ms * 1e-3)        # this rank's kernel
+    peaks = {}
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except (OSError, ValueError):
         pass
-    roof = {"bound": "hbm", "unit": "GB/s", "peak": hbm_peak, "peak_source": peak_src, "traffic": traffic,
-            "kernel": {"bf": "stencil_kernel<BF>", "abf": "stencil_kernel<ABF>", "btf": "stencil_kernel<JBF>", "all": "stencil_kernel<JBF>"}[filt],
-            "note": "the bilateral stencils are instruction-issue bound (see 'issue'); HBM traffic is 6-9 B/pixel"}
-    roof["achieved"] = alg_bytes / (kernel_ms * 1e-3) / 1e9
-    roof["frac"] = roof["achieved"] / hbm_peak
-    roof["kernel_ms"] = kernel_ms
-    sm_mhz = clocks.get("sm_mhz") or float(peaks.get("sm_max_mhz", 1965.0))
-    sm_count = torch.cuda.get_device_properties(local_rank).multi_processor_count
-    taps_s = local_pixels * taps / (kernel_ms * 1e-3)    # of the dominant kernel, from its own live timing
-    issue_peak = sm_count * 4 * 32 * sm_mhz * 1e6        # thread-instructions / s at the sampled clock
-    issue = {"kernel": roof["kernel"], "kernel_ms": kernel_ms, "taps_per_pixel": taps, "step_taps_per_pixel": taps_per_px,
-             "gtaps_per_s": taps_s / 1e9, "est_instr_per_tap": instr_per_tap,
-             "est_issue_util": taps_s * instr_per_tap / issue_peak, "sm_mhz_used": sm_mhz,
-             "peak_thread_instr_per_s": issue_peak,
-             "note": "taps/s x SASS instructions per tap (ncu smsp__inst_executed of the same kernel, profiles/) / (SMs x 4 x 32 x clock); packed fp32x2 instructions count once here but hold the dispatch port twice, see DESIGN.md 3"}
-    # measured issue roofs (SURVEY.md 8d asks for an FFMA micro-kernel on the box): tools/probe/issue_probe.cu, a few ms each
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    ncu = {}
     try:
-        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        ncu = json.load(open(os.path.join(ROOT, "profiles", "ncu_constants.json"))).get("stencil_" + kind, {})
+    except (OSError, ValueError):
+        pass
+    roof = {"bound": "issue", "unit": "thread-instr/s",
+            "kernel": {"bf": "stencil_kernel<BF>", "abf": "stencil_kernel<ABF>", "jbf": "stencil_kernel<JBF>"}[kind],
+            "kernel_ms": kernel_ms, "taps_per_pixel": taps, "taps_per_s": taps_s, "i_min_per_tap": imin, "outputs_per_thread": P,
+            "achieved": taps_s * imin, "peak": None, "frac": None,
+            "definition": "achieved = taps/s x I_min (SURVEY.md 8d: BF 7+4/P, JBF 7+5/P, ABF 15+4/P thread-instructions per tap); peak = FFMA issue rate measured live on this GPU (tools/probe/issue_probe.cu); MEASURED_PEAKS.json has no FP32 / issue figure",
+            "traffic": ncu.get("dram_bytes_per_launch"),
+            "hbm": {"achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                    "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)",
+                    "algorithmic_bytes_per_launch": alg_bytes}}
+    roof["hbm"]["frac"] = roof["hbm"]["achieved"] / hbm_peak
+    roof["fp32"] = {"achieved_tflops": taps_s * FLOP_PER_TAP[kind] / 1e12, "flop_per_tap": FLOP_PER_TAP[kind]}
+    issue = {"util_ncu": ncu or None}
+    try:
         import peaks as _peaks
         _pl = _peaks.load()
-        if _pl is not None and rank == 0 and not args.no_probe:
+        if _pl is not None and not ctx.args.no_probe:
             ffma, _ = _peaks.measure(_pl, 0)
-            ffma2, _ = _peaks.measure(_pl, 1)
-            issue["measured_ffma_thread_instr_per_s"] = ffma
-            issue["measured_ffma2_packed_instr_per_s"] = ffma2
-            # a packed fp32x2 instruction holds the dispatch port for two slots (measured: the FFMA2 rate is half the FFMA
-            # rate), so the slots a tap costs are instr + packed; their rate against the measured FFMA rate is the fraction of
-            # the stencil's own roofline -- the number to read instead of roofline.frac for these kernels
-            issue["packed_instr_per_tap"] = packed_per_tap
-            issue["dispatch_slots_per_tap"] = instr_per_tap + packed_per_tap
-            issue["frac_of_measured_issue_roof"] = taps_s * (instr_per_tap + packed_per_tap) / ffma
-            # the same inside the roofline object, for a reader who looks only there: the bound that binds this kernel
-            roof["relevant"] = {"bound": "issue", "unit": "thread-instr/s", "achieved": taps_s * (instr_per_tap + packed_per_tap),
-                                "peak": ffma, "peak_source": "measured live (tools/probe/issue_probe.cu, FFMA)",
-                                "frac": issue["frac_of_measured_issue_roof"]}
-    except Exception as exc:                                 # the probe is optional evidence, never a reason to fail the bench
+            roof["peak"] = ffma
+            roof["peak_source"] = "measured live: FFMA thread-instructions/s (tools/probe/issue_probe.cu)"
+            roof["frac"] = roof["achieved"] / ffma
+            roof["fp32"]["peak_tflops"] = 2 * ffma / 1e12
+            roof["fp32"]["frac"] = roof["fp32"]["achieved_tflops"] / roof["fp32"]["peak_tflops"]
+    except Exception as exc:                                 # the probe is evidence, never a reason to fail the bench
         issue["probe_error"] = str(exc)
-
-    cpu = None
-    if not args.no_cpu_baseline:
-        rows = sample_rows_for(filt, w, h, ksize)
-        mp, kind, cores, what, _ = cpu_reference(filt, w, h, ksize, nitr, rows, args.cpu_threads, repeats=2)
-        cpu = {"value": mp, "unit": "Mpixel/s", "cores": cores, "kind": kind, "sample": what}
+    if roof["peak"] is None:                                 # nominal issue rate at the max clock, said so
+        nominal = ctx.sm_count * 128 * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6
+        roof["peak"], roof["peak_source"] = nominal, "nominal: SMs x 128 thread-instr/clk x max SM clock (probe not run)"
+        roof["frac"] = roof["achieved"] / nominal
 
     out = {
-        "metric": f"{filt}_throughput", "value": value, "unit": "Mpixel/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if strong else "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "description": desc, "width": w, "height": h, "ksize": ksize, "nitr": nitr,
-                   "content": args.content, "parallelism": ("row strips + halos" if strong else f"{world} independent frame stream(s)"),
-                   "l2": f"rotating over {n_pool} distinct resident frames ({2 * n_pool * w * (s1 - s0) * 3 >> 20} MiB in+out > 126 MiB L2)",
-                   "e2e": "pinned host buffers, upload + filter + download per step, four frames in flight on four streams"},
-        "e2e": {"value": e2e_value, "unit": "Mpixel/s", "h2d_bytes_per_step": w * (s1 - s0) * 3 * world,
-                "d2h_bytes_per_step": w * out_rows * 3 * world * n_out, "steps": e2e_steps},
-        "gpu_launches": int(launches), "kernels_per_step": kernels_per_step,
-        "roofline": roof, "issue": issue, "cpu_baseline": cpu, "clocks": clocks,
+        "metric": f"{filt}_throughput", "value": value, "unit": "Mpixel/s", "ms_per_step": ms_step, "steps": steps, "warmup": warmup,
+        "scaling": "strong" if job.strong else "weak",
+        "config": {"workload": name, "description": job.desc, "width": w, "height": h, "ksize": ksize, "nitr": nitr,
+                   "content": ctx.args.content,
+                   "parallelism": (f"{ctx.world} row strips of one frame, one process per {'rank (ranks SHARE a GPU: functional test, not a measurement)' if ctx.shared_gpu else 'GPU'}; halo {job.halo} rows per side; {job.transport}"
+                                   if job.strong else f"{ctx.world} independent frame stream(s)"),
+                   "l2": f"rotating over {job.n_pool} distinct resident frames ({2 * job.n_pool * job.rb * job.own >> 20} MiB in+out per GPU > 126 MiB L2)",
+                   "e2e": f"pinned host buffers; per step every rank uploads its own rows, filters, downloads its rows; {NS} frames in flight on {NS} streams; neighbours ordered by device-side flags (vip_link_*)"},
+        "e2e": {"value": e2e_value, "unit": "Mpixel/s", "h2d_bytes_per_step": job.rb * (h if job.strong else h * ctx.world),
+                "d2h_bytes_per_step": job.rb * (h if job.strong else h * ctx.world) * job.n_out, "steps": e2e_steps,
+                "ms_per_step": e2e_s * 1e3,
+                "copy_ceiling": {"value": pixels_step / ceil_s / 1e6, "unit": "Mpixel/s", "ms_per_step": ceil_s * 1e3,
+                                 "gbs_each_way": job.rb * (h if job.strong else h * ctx.world) / ceil_s / 1e9,
+                                 "what": "the same pinned uploads + downloads on the same streams with no kernels, all ranks at once"},
+                "frac_of_copy_ceiling": ceil_s / e2e_s},
+        "gpu_launches": int(launches), "kernels_per_step": launches / max(steps, 1),
+        "dominant_kernel_launches_per_step": launches_of_kernel_per_step,
+        "roofline": roof, "issue": issue, "_marks": (marks[0], marks[1], mark_end),
     }
-    print(json.dumps(out), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    if parity is not None:
+        out["strip_parity"] = parity["verdict"]
+        out["parity"] = parity
+    if ref_cuda is not None:
+        ref_cuda["speedup_whole_job"] = ref_cuda["ms"] / ms_step
+        out["ref_cuda"] = ref_cuda
+    if with_cpu:
+        rows = sample_rows_for(filt, w, h, ksize, cpu_budget)
+        mp, ckind, cores, what, _ = cpu_reference(filt, w, h, ksize, nitr, rows, ctx.args.cpu_threads, repeats=2, content=ctx.args.content)
+        out["cpu_baseline"] = {"value": mp, "unit": "Mpixel/s", "cores": cores, "kind": ckind, "sample": what}
+    return out, job
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-threads", type=int, default=0, help="threads of the CPU baseline (0 = all host cores)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-probe", action="store_true", help="skip the issue-rate probe kernels (for ncu launch lists)")
+    ap.add_argument("--no-per-workload", action="store_true", help="only the main workload (for ncu / quick runs)")
+    ap.add_argument("--content", default="rand", choices=["rand", "narrow", "nat", "smooth"], help="synthetic content (SURVEY.md 8d)")
+    ap.add_argument("--halo", default="fused", choices=["fused", "copy"],
+                    help="N > 1: halo rows staged by the kernel from the neighbours' memory, or pulled by peer copies")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference_arm(args, WORKLOADS[args.workload])
+        return
+
+    ctx = Ctx(args)
+    sampler = ClockSampler(ctx.device_index)
+    sampler.start()
+    time.sleep(0.2)
+    main_out, job = measure_job(ctx, args.workload, args.steps, args.warmup, args.halo, sampler=sampler,
+                                with_cpu=not args.no_cpu_baseline and ctx.world == 1)
+    if main_out is not None:
+        m0, m1, m2 = main_out.pop("_marks")
+        # the timed region alone can be shorter than two sampling periods (20 steps x 0.9 ms at N = 8): then the window is
+        # widened to the device-timed region + the end-to-end leg that follows it, and the line says so
+        if m1 - m0 >= 3:
+            clocks = sampler.stop(m0, m1 + 1)
+            clocks["window"] = "device-timed region"
+        else:
+            clocks = sampler.stop(max(0, m0 - 1), m2 + 1)
+            clocks["window"] = "device-timed region + end-to-end leg (the timed region alone spans < 3 samples of 50 ms)"
+    else:
+        clocks = sampler.stop()
+    del job
+    per = {}
+    if not args.no_per_workload and args.workload == DEFAULT_WORKLOAD:
+        for name in PER_WORKLOAD:
+            try:
+                o, j = measure_job(ctx, name, 20, 3, args.halo, with_cpu=not args.no_cpu_baseline and ctx.world == 1, cpu_budget=4e8)
+                del j
+                if o is not None:
+                    for k in ("steps", "warmup", "gpu_launches", "kernels_per_step", "issue", "_marks"):
+                        o.pop(k, None)
+                    per[name] = o
+            except Exception as exc:       # a side workload never takes the headline down; it is reported instead
+                per[name] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+                ctx.barrier()
+    if ctx.rank == 0:
+        out = {"metric": main_out.pop("metric"), "value": main_out.pop("value"), "unit": main_out.pop("unit"), "n_gpus": ctx.world,
+               "steps": main_out.pop("steps"), "warmup": main_out.pop("warmup"), "ms_per_step": main_out.pop("ms_per_step"),
+               "higher_is_better": True, "scaling": main_out.pop("scaling"), "vs_baseline": None, "dtype": "f32",
+               "data": "lenna.png" if args.workload == "bf_lenna" else "synthetic"}
+        out.update(main_out)
+        out["clocks"] = clocks
+        out["host_placement"] = ctx.placement
+        if per:
+            out["per_workload"] = per
+        print(json.dumps(out), flush=True)
+    if ctx.world > 1:
+        ctx.dist.destroy_process_group()
 
 
 if __name__ == "__main__":

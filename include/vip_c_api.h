@@ -19,7 +19,9 @@
  *   - `d_` pointers are device pointers on the CURRENT device; `stream` is a cudaStream_t passed as void*
  *     (NULL = legacy default stream).  All run calls are asynchronous with respect to the host; the C++
  *     wrappers add the cudaDeviceSynchronize() the reference performs after every public call.
- *   - in-place operation (d_src == d_dst) is not supported (same as the reference).
+ *   - in-place operation (d_src == d_dst) is not supported by the bilateral / adaptive bilateral filters (same as the
+ *     reference: neighbours are read while outputs are written); the bilateral texture filter accepts it, like the
+ *     reference, whose execute() copies the source into its own buffers first.
  *   - ksize must be odd and >= 1 (the reference silently misbehaves for even ksize, SURVEY.md 9.4;
  *     VIP_E_KSIZE is returned instead).
  *
@@ -72,6 +74,18 @@ typedef struct vip_strip {
     int out_rows;
 } vip_strip;
 
+/* Where the halo rows of a strip come from when the strip buffer holds only the rank's OWN rows (one process per
+ * GPU): device pointers into the buffers of the ranks above / below -- peer pointers of the same process or pointers
+ * opened with vip_ipc_open() -- and the image rows those buffers hold.  NULL = no neighbour on that side (the image
+ * border: rows clamp).  The *_strip_peer entry points stage these rows straight from the neighbour's memory inside the
+ * filter kernel (NVLink loads): no halo copy, no halo rows in the local buffer. */
+typedef struct vip_halo {
+    const uint8_t* d_above;
+    int above_y0, above_rows;
+    const uint8_t* d_below;
+    int below_y0, below_rows;
+} vip_halo;
+
 /* ---- library ------------------------------------------------------------------------------------------ */
 VIP_API const char* vip_version(void);
 /* Human-readable text for a status returned by any function of this header. */
@@ -104,6 +118,10 @@ VIP_API int vip_image_upload(vip_image* img, const void* host_data);
 VIP_API int vip_image_download(const vip_image* img, void* host_data);
 VIP_API int vip_image_upload_async(vip_image* img, const void* host_data, void* stream);
 VIP_API int vip_image_download_async(const vip_image* img, void* host_data, void* stream);
+/* Whole rows [row0, row0 + rows) of the image <-> a packed host buffer of rows * width * channels elements (the own rows
+ * of a strip buffer that also has room for halo rows). */
+VIP_API int vip_image_upload_rows_async(vip_image* img, const void* host_rows, int row0, int rows, void* stream);
+VIP_API int vip_image_download_rows_async(const vip_image* img, void* host_rows, int row0, int rows, void* stream);
 VIP_API void* vip_image_data(const vip_image* img);
 VIP_API size_t vip_image_bytes(const vip_image* img);
 /* pinned host memory for the async copies */
@@ -128,6 +146,10 @@ VIP_API int vip_bf_run_strip(const vip_bf* f, const uint8_t* d_src, uint8_t* d_d
                              void* stream);
 VIP_API int vip_jbf_run_strip(const vip_bf* f, const uint8_t* d_src, const uint8_t* d_guide, uint8_t* d_dst,
                               const vip_strip* strip, void* stream);
+/* Strip whose halo rows are read from the neighbouring ranks' device memory (see struct vip_halo).  src rows + halo
+ * rows together must cover [out_y0 - radius, out_y0 + out_rows + radius) clipped to the image. */
+VIP_API int vip_bf_run_strip_peer(const vip_bf* f, const uint8_t* d_src, const vip_halo* halo, uint8_t* d_dst,
+                                  const vip_strip* strip, void* stream);
 VIP_API int vip_bf_halo_rows(const vip_bf* f); /* = ksize/2 */
 /* Copies of the tables the object holds (for tests): kernel_space is ksize*ksize floats, color_table 768. */
 VIP_API int vip_bf_get_luts(const vip_bf* f, float* kernel_space, float* color_table);
@@ -144,6 +166,8 @@ VIP_API int vip_abf_destroy(vip_abf* f);
 VIP_API int vip_abf_run(const vip_abf* f, const uint8_t* d_src, uint8_t* d_dst, void* stream);
 VIP_API int vip_abf_run_strip(const vip_abf* f, const uint8_t* d_src, uint8_t* d_dst, const vip_strip* strip,
                               void* stream);
+VIP_API int vip_abf_run_strip_peer(const vip_abf* f, const uint8_t* d_src, const vip_halo* halo, uint8_t* d_dst,
+                                   const vip_strip* strip, void* stream);
 VIP_API int vip_abf_halo_rows(const vip_abf* f); /* = ksize/2 */
 
 /* ---- gradient magnitude -------------------------------------------------------------------------------
@@ -268,6 +292,43 @@ VIP_API int vip_mg_last_run_ms(const vip_mg* m, float* ms);
 /* Independent frames: frame f goes to device slot f % n.  h_src/h_dst hold n_frames packed images (pinned memory
  * recommended).  Uploads, kernels and downloads of different frames overlap on two streams per device. */
 VIP_API int vip_mg_run_batch_host(vip_mg* m, const uint8_t* h_src, uint8_t* h_dst, int n_frames);
+
+/* ---- one process per GPU: cross-process device memory and neighbour ordering (csrc/link.cu) -------------------
+ * Under torchrun every rank owns one GPU and one row strip.  vip_ipc_export() turns a device allocation (the base
+ * pointer of a vip_image, or of any cudaMalloc'ed buffer) into a 64-byte handle that another PROCESS of the same box
+ * opens with vip_ipc_open(); the pointer it gets is an ordinary device pointer there (peer-to-peer over NVLink when the
+ * two ranks sit on different GPUs).  VIP_E_DEVICE: the two devices have no peer path -- pick another transport, nothing
+ * falls back silently.  vip_copy_rows() is the explicit halo pull (one asynchronous copy of whole rows). */
+#define VIP_IPC_HANDLE_BYTES 64
+VIP_API int vip_ipc_export(const void* d_ptr, unsigned char* handle /* [VIP_IPC_HANDLE_BYTES] */);
+VIP_API int vip_ipc_open(const unsigned char* handle, void** d_ptr);
+VIP_API int vip_ipc_close(void* d_ptr);
+VIP_API int vip_peer_can_access(int device, int peer_device); /* 1 / 0 */
+VIP_API int vip_copy_rows(uint8_t* d_dst, int dst_y0, const uint8_t* d_src, int src_y0, int y0, int rows, int width,
+                          void* stream);
+/* Ordering between a rank and its two strip neighbours without the host: step numbers stored into the neighbour's flag
+ * block by a one-thread kernel, waits polling the rank's own block -- all enqueued on streams.
+ *   ready(slot, step)     "my own rows of `step` are in buffer `slot`"          (after the upload / the producing kernel)
+ *   consumed(slot, step)  "I have finished reading your rows of `step`"         (after the filter kernel)
+ * A frame pipeline with n_slots buffers in flight runs, per step s on slot s % n_slots:
+ *   wait_consumed(slot, s - n_slots) ; upload own rows ; signal_ready(slot, s) ; wait_ready(slot, s) ;
+ *   filter (halo rows from the neighbours) ; signal_consumed(slot, s) ; download.
+ * Steps count from 1.  A wait that sees no progress for the timeout (default 2000 ms of device time) gives up and
+ * latches an error that vip_link_status() returns as VIP_E_DEVICE. */
+typedef struct vip_link vip_link;
+VIP_API int vip_link_create(vip_link** out, int n_slots);
+VIP_API int vip_link_destroy(vip_link* l);
+VIP_API int vip_link_export(const vip_link* l, unsigned char* handle /* [VIP_IPC_HANDLE_BYTES] */);
+/* handles of the ranks above / below (NULL at the image border), as exported by THEIR vip_link_export */
+VIP_API int vip_link_connect(vip_link* l, const unsigned char* above_handle, const unsigned char* below_handle);
+/* the same inside one process (several ranks of a test, or devices driven by one process) */
+VIP_API int vip_link_connect_local(vip_link* l, vip_link* above, vip_link* below);
+VIP_API int vip_link_set_timeout_ms(vip_link* l, int timeout_ms);
+VIP_API int vip_link_signal_ready(vip_link* l, int slot, unsigned step, void* stream);
+VIP_API int vip_link_wait_ready(vip_link* l, int slot, unsigned step, void* stream);
+VIP_API int vip_link_signal_consumed(vip_link* l, int slot, unsigned step, void* stream);
+VIP_API int vip_link_wait_consumed(vip_link* l, int slot, unsigned step, void* stream);
+VIP_API int vip_link_status(vip_link* l);
 
 #ifdef __cplusplus
 }

@@ -11,7 +11,8 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "tools", "probe", "libvip_probe.so")
-KINDS = {0: "ffma", 1: "ffma2_packed", 2: "ffma_plus_vabsdiff4", 3: "lds32", 4: "i2f_u8"}
+KINDS = {0: "ffma", 1: "ffma2_packed", 2: "ffma_plus_vabsdiff4", 3: "lds32", 4: "i2f_u8", 5: "ffma2_plus_vabsdiff4",
+         6: "ffma2_plus_lds32", 7: "ffma_plus_lop3", 8: "ffma2_plus_ffma"}
 
 
 def load():

@@ -7,6 +7,10 @@
 //   2  FFMA + VABSDIFF4  alternating fp32 (FMA pipe) and the packed-byte SAD of the range index (ALU pipe): do they overlap?
 //   3  LDS.32          conflict-free shared-memory loads (lane l reads word l of a 32-word row)
 //   4  I2F.U8          byte -> float conversion (the XU-pipe instruction of the tile unpack)
+//   5  FFMA2 + VABSDIFF4 alternating: does a packed FMA block the dispatch port for the ALU pipe too, or only the FMA pipe?
+//   6  FFMA2 + LDS.32    alternating: the same question for the LSU
+//   7  FFMA + LOP3       alternating (FMA pipe + a plain ALU instruction)
+//   8  FFMA2 + FFMA      alternating (packed and scalar FMAs sharing the FMA pipe)
 // Not part of the product library: built by __graft_entry__.build() into tools/probe/libvip_probe.so and called by
 // bench.py (key "issue.measured_peak") and tools/peaks.py through ctypes.
 #include <cuda_runtime.h>
@@ -33,7 +37,7 @@ __global__ void __launch_bounds__(kThreads, 1) probe_kernel(float* __restrict__ 
     for (int c = 0; c < kChains; ++c) {
         a[c] = seed + c + threadIdx.x;
         asm("mov.b64 %0, {%1, %1};" : "=l"(p[c]) : "f"(a[c]));
-        u[c] = KIND == 3 ? lane_addr + (((threadIdx.x >> 5) * 5u + c) & 31u) * 132u : threadIdx.x * 2654435761u + c;
+        u[c] = (KIND == 3 || (KIND == 6 && !(c & 1))) ? lane_addr + (((threadIdx.x >> 5) * 5u + c) & 31u) * 132u : threadIdx.x * 2654435761u + c;
     }
     const float m = 0.999f + seed * 1e-9f, b = seed * 1e-3f;
     unsigned long long m2, b2;
@@ -53,6 +57,29 @@ __global__ void __launch_bounds__(kThreads, 1) probe_kernel(float* __restrict__ 
                         asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[c]) : "f"(m), "f"(b));
                     else
                         asm volatile("vabsdiff4.u32.u32.u32.add %0, %0, %1, %0;" : "+r"(u[c]) : "r"(u[(c + 2) % kChains]));
+                } else if constexpr (KIND == 5) {
+                    if (c & 1)
+                        asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(p[c]) : "l"(m2), "l"(b2));
+                    else
+                        asm volatile("vabsdiff4.u32.u32.u32.add %0, %0, %1, %0;" : "+r"(u[c]) : "r"(u[(c + 2) % kChains]));
+                } else if constexpr (KIND == 6) {
+                    if (c & 1) {
+                        asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(p[c]) : "l"(m2), "l"(b2));
+                    } else {
+                        float v;
+                        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(u[c]));
+                        u[c] += __float_as_uint(v) >> 31;
+                    }
+                } else if constexpr (KIND == 7) {
+                    if (c & 1)
+                        asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[c]) : "f"(m), "f"(b));
+                    else
+                        asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(u[c]) : "r"(u[(c + 2) % kChains]), "r"(0x5bd1e995u));
+                } else if constexpr (KIND == 8) {
+                    if (c & 1)
+                        asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[c]) : "f"(m), "f"(b));
+                    else
+                        asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(p[c]) : "l"(m2), "l"(b2));
                 } else if constexpr (KIND == 3) {
                     // the row is warp-uniform (pitch 33 words: lane l hits bank (row + l) % 32, conflict-free); the next
                     // address depends on the loaded value's sign bit (always 0), which keeps the chain honest
@@ -72,7 +99,7 @@ __global__ void __launch_bounds__(kThreads, 1) probe_kernel(float* __restrict__ 
     for (int c = 0; c < kChains; ++c) {
         float lo, hi;
         asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(p[c]));
-        acc += a[c] + lo + hi + __uint_as_float(u[c] & 0x3fffffffu) + (KIND == 3 ? lds_src[u[c] & 31u] : 0.f);
+        acc += a[c] + lo + hi + __uint_as_float(u[c] & 0x3fffffffu) + ((KIND == 3 || KIND == 6) ? lds_src[u[c] & 31u] : 0.f);
     }
     if (acc == 123.456f) sink[0] = acc;  // never true in practice: keeps the chains alive
 }
@@ -105,6 +132,10 @@ extern "C" __attribute__((visibility("default"))) int vip_probe_issue_rate(int k
             case 2: return run_kind<2>(sink, sms, n, nullptr);
             case 3: return run_kind<3>(sink, sms, n, nullptr);
             case 4: return run_kind<4>(sink, sms, n, nullptr);
+            case 5: return run_kind<5>(sink, sms, n, nullptr);
+            case 6: return run_kind<6>(sink, sms, n, nullptr);
+            case 7: return run_kind<7>(sink, sms, n, nullptr);
+            case 8: return run_kind<8>(sink, sms, n, nullptr);
             default: return cudaErrorInvalidValue;
         }
     };
@@ -121,7 +152,7 @@ extern "C" __attribute__((visibility("default"))) int vip_probe_issue_rate(int k
     cudaEventDestroy(e1);
     cudaFree(sink);
     if (e != cudaSuccess) return e;
-    // KIND 3 / 4 carry one dependent integer instruction per probe instruction; it is not counted
+    // KIND 3 / 4 (and the LDS half of 6) carry one dependent integer instruction per probe instruction; it is not counted
     const double n_instr = static_cast<double>(sms) * kThreads * static_cast<double>(trips) * kUnroll * kChains;
     if (instr_per_s) *instr_per_s = n_instr / (ms * 1e-3);
     if (elapsed_ms) *elapsed_ms = ms;

@@ -18,6 +18,7 @@ VIP_LUT_CUDA, VIP_LUT_CPU = 0, 1
 VIP_MG_BF, VIP_MG_ABF, VIP_MG_BTF = 0, 1, 2
 VIP_MG_FLAG_BTF_EXCHANGE, VIP_MG_FLAG_BTF_DEEP_HALO = 1, 2
 VIP_SRC_U8, VIP_SRC_U16, VIP_SRC_F32 = 0, 1, 2
+VIP_IPC_HANDLE_BYTES = 64
 
 
 class VipError(RuntimeError):
@@ -30,6 +31,12 @@ class Strip(C.Structure):
     """struct vip_strip: rows held by the buffers and rows to produce (all in full-image row numbers)."""
     _fields_ = [("src_y0", C.c_int), ("src_rows", C.c_int), ("dst_y0", C.c_int), ("out_y0", C.c_int),
                 ("out_rows", C.c_int)]
+
+
+class Halo(C.Structure):
+    """struct vip_halo: the neighbouring ranks' buffers a *_strip_peer call stages its halo rows from."""
+    _fields_ = [("d_above", C.c_void_p), ("above_y0", C.c_int), ("above_rows", C.c_int),
+                ("d_below", C.c_void_p), ("below_y0", C.c_int), ("below_rows", C.c_int)]
 
 
 class StencilPlan(C.Structure):
@@ -59,6 +66,8 @@ SIGNATURES = {
     "vip_image_download": (_i, [_vp, _vp]),
     "vip_image_upload_async": (_i, [_vp, _vp, _vp]),
     "vip_image_download_async": (_i, [_vp, _vp, _vp]),
+    "vip_image_upload_rows_async": (_i, [_vp, _vp, _i, _i, _vp]),
+    "vip_image_download_rows_async": (_i, [_vp, _vp, _i, _i, _vp]),
     "vip_image_data": (_vp, [_vp]),
     "vip_image_bytes": (_sz, [_vp]),
     "vip_host_alloc": (_i, [_pp, _sz]),
@@ -72,6 +81,7 @@ SIGNATURES = {
     "vip_jbf_run": (_i, [_vp, _vp, _vp, _vp, _vp]),
     "vip_bf_run_strip": (_i, [_vp, _vp, _vp, C.POINTER(Strip), _vp]),
     "vip_jbf_run_strip": (_i, [_vp, _vp, _vp, _vp, C.POINTER(Strip), _vp]),
+    "vip_bf_run_strip_peer": (_i, [_vp, _vp, C.POINTER(Halo), _vp, C.POINTER(Strip), _vp]),
     "vip_bf_halo_rows": (_i, [_vp]),
     "vip_bf_get_luts": (_i, [_vp, _vp, _vp]),
     "vip_abf_create": (_i, [_pp, _i, _i, _i, _f, _f]),
@@ -79,6 +89,7 @@ SIGNATURES = {
     "vip_abf_destroy": (_i, [_vp]),
     "vip_abf_run": (_i, [_vp, _vp, _vp, _vp]),
     "vip_abf_run_strip": (_i, [_vp, _vp, _vp, C.POINTER(Strip), _vp]),
+    "vip_abf_run_strip_peer": (_i, [_vp, _vp, C.POINTER(Halo), _vp, C.POINTER(Strip), _vp]),
     "vip_abf_halo_rows": (_i, [_vp]),
     "vip_gradient_u8": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "vip_gradient_f32": (_i, [_vp, _vp, _i, _i, _i, _vp]),
@@ -112,6 +123,22 @@ SIGNATURES = {
     "vip_mg_gather_host": (_i, [_vp, _vp]),
     "vip_mg_last_run_ms": (_i, [_vp, C.POINTER(C.c_float)]),
     "vip_mg_run_batch_host": (_i, [_vp, _vp, _vp, _i]),
+    "vip_ipc_export": (_i, [_vp, _vp]),
+    "vip_ipc_open": (_i, [_vp, _pp]),
+    "vip_ipc_close": (_i, [_vp]),
+    "vip_peer_can_access": (_i, [_i, _i]),
+    "vip_copy_rows": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _vp]),
+    "vip_link_create": (_i, [_pp, _i]),
+    "vip_link_destroy": (_i, [_vp]),
+    "vip_link_export": (_i, [_vp, _vp]),
+    "vip_link_connect": (_i, [_vp, _vp, _vp]),
+    "vip_link_connect_local": (_i, [_vp, _vp, _vp]),
+    "vip_link_set_timeout_ms": (_i, [_vp, _i]),
+    "vip_link_signal_ready": (_i, [_vp, _i, C.c_uint, _vp]),
+    "vip_link_wait_ready": (_i, [_vp, _i, C.c_uint, _vp]),
+    "vip_link_signal_consumed": (_i, [_vp, _i, C.c_uint, _vp]),
+    "vip_link_wait_consumed": (_i, [_vp, _i, C.c_uint, _vp]),
+    "vip_link_status": (_i, [_vp]),
 }
 
 _lib = None

@@ -139,23 +139,42 @@ int init_tables(StencilTables& T, int width, int height, int ksize, float ss, fl
     return VIP_OK;
 }
 
-// Rows [out_y0-halo, out_y0+out_rows+halo) clipped to the image must lie inside the source buffer.
-int check_strip(const vip_strip& s, int height, int halo) {
+// Rows [out_y0-halo, out_y0+out_rows+halo) clipped to the image must lie inside the source buffer -- or, with peer
+// halos, inside the union of the neighbour-above rows, the source buffer and the neighbour-below rows.
+int check_strip(const vip_strip& s, int height, int halo, const vip_halo* peer = nullptr) {
     if (s.out_rows < 0 || s.src_rows <= 0) return VIP_E_STRIP;
     if (s.out_rows == 0) return VIP_OK;
     if (s.out_y0 < 0 || s.out_y0 + s.out_rows > height) return VIP_E_STRIP;
-    if (s.dst_y0 > s.out_y0 || s.dst_y0 < 0) return VIP_E_STRIP;
+    if (s.dst_y0 > s.out_y0 || s.dst_y0 < 0 || s.src_y0 < 0) return VIP_E_STRIP;
     const int need0 = std::max(0, s.out_y0 - halo), need1 = std::min(height, s.out_y0 + s.out_rows + halo);
-    if (s.src_y0 > need0 || s.src_y0 + s.src_rows < need1 || s.src_y0 < 0) return VIP_E_STRIP;
+    int have0 = s.src_y0, have1 = s.src_y0 + s.src_rows;
+    if (peer && peer->d_above) {
+        if (peer->above_rows <= 0 || peer->above_y0 < 0 || peer->above_y0 + peer->above_rows < have0) return VIP_E_STRIP;
+        have0 = std::min(have0, peer->above_y0);
+    }
+    if (peer && peer->d_below) {
+        if (peer->below_rows <= 0 || peer->below_y0 > have1) return VIP_E_STRIP;
+        have1 = std::max(have1, peer->below_y0 + peer->below_rows);
+    }
+    if (have0 > need0 || have1 < need1) return VIP_E_STRIP;
+    // the centre pixels (and the ABF box of the outputs) are read from the local buffer: outputs must be own rows
+    if (peer && (s.out_y0 < s.src_y0 || s.out_y0 + s.out_rows > s.src_y0 + s.src_rows)) return VIP_E_STRIP;
     return VIP_OK;
 }
 
 int run_stencil(const StencilTables& T, vip::StencilMode mode, const uint8_t* d_src, const uint8_t* d_guide,
-                uint8_t* d_dst, const vip_strip& s, void* stream) {
+                uint8_t* d_dst, const vip_strip& s, void* stream, const vip_halo* peer = nullptr) {
     if (!d_src || !d_dst || (mode == vip::kJBF && !d_guide)) return VIP_E_NULL;
-    const int c = check_strip(s, T.height, T.radius);
+    if (peer && mode == vip::kJBF) return VIP_E_UNSUPPORTED;
+    const int c = check_strip(s, T.height, T.radius, peer);
     if (c != VIP_OK) return c;
     vip::StencilArgs a;
+    a.above = peer ? peer->d_above : nullptr;
+    a.below = peer ? peer->d_below : nullptr;
+    a.above_y0 = peer ? peer->above_y0 : 0;
+    a.above_rows = peer ? peer->above_rows : 0;
+    a.below_y0 = peer ? peer->below_y0 : 0;
+    a.below_rows = peer ? peer->below_rows : 0;
     a.src = d_src;
     a.guide = d_guide;
     a.dst = d_dst;
@@ -192,7 +211,7 @@ struct vip_image {
 struct vip_btf {
     int width, height, ksize, nitr, scratch_rows;
     vip_bf* jbf;
-    DeviceBuf ping, pong, blurred, magnitude, rtv, guide;
+    DeviceBuf ping, pong, blurred, rtv, guide;
 };
 
 extern "C" {
@@ -282,6 +301,20 @@ int vip_image_download_async(const vip_image* img, void* h, void* stream) {
     if (!img || !h) return VIP_E_NULL;
     return cu(cudaMemcpyAsync(h, img->buf.p, img->buf.bytes, cudaMemcpyDeviceToHost, static_cast<cudaStream_t>(stream)));
 }
+int vip_image_upload_rows_async(vip_image* img, const void* h, int row0, int rows, void* stream) {
+    if (!img || !h) return VIP_E_NULL;
+    if (row0 < 0 || rows < 0 || row0 + rows > img->height) return VIP_E_SIZE;
+    const size_t rb = static_cast<size_t>(img->width) * img->channels * img->elem_size;
+    return cu(cudaMemcpyAsync(static_cast<char*>(img->buf.p) + rb * row0, h, rb * rows, cudaMemcpyHostToDevice,
+                              static_cast<cudaStream_t>(stream)));
+}
+int vip_image_download_rows_async(const vip_image* img, void* h, int row0, int rows, void* stream) {
+    if (!img || !h) return VIP_E_NULL;
+    if (row0 < 0 || rows < 0 || row0 + rows > img->height) return VIP_E_SIZE;
+    const size_t rb = static_cast<size_t>(img->width) * img->channels * img->elem_size;
+    return cu(cudaMemcpyAsync(h, static_cast<const char*>(img->buf.p) + rb * row0, rb * rows, cudaMemcpyDeviceToHost,
+                              static_cast<cudaStream_t>(stream)));
+}
 void* vip_image_data(const vip_image* img) { return img ? img->buf.p : nullptr; }
 size_t vip_image_bytes(const vip_image* img) { return img ? img->buf.bytes : 0; }
 int vip_host_alloc(void** out, size_t bytes) {
@@ -330,6 +363,11 @@ int vip_jbf_run_strip(const vip_bf* f, const uint8_t* d_src, const uint8_t* d_gu
     if (!f || !strip) return VIP_E_NULL;
     return run_stencil(f->T, vip::kJBF, d_src, d_guide, d_dst, *strip, stream);
 }
+int vip_bf_run_strip_peer(const vip_bf* f, const uint8_t* d_src, const vip_halo* halo, uint8_t* d_dst,
+                          const vip_strip* strip, void* stream) {
+    if (!f || !strip || !halo) return VIP_E_NULL;
+    return run_stencil(f->T, vip::kBF, d_src, nullptr, d_dst, *strip, stream, halo);
+}
 int vip_bf_halo_rows(const vip_bf* f) { return f ? f->T.radius : VIP_E_NULL; }
 int vip_bf_get_luts(const vip_bf* f, float* kernel_space, float* color_table) {
     if (!f) return VIP_E_NULL;
@@ -366,6 +404,11 @@ int vip_abf_run(const vip_abf* f, const uint8_t* d_src, uint8_t* d_dst, void* st
 int vip_abf_run_strip(const vip_abf* f, const uint8_t* d_src, uint8_t* d_dst, const vip_strip* strip, void* stream) {
     if (!f || !strip) return VIP_E_NULL;
     return run_stencil(f->T, vip::kABF, d_src, nullptr, d_dst, *strip, stream);
+}
+int vip_abf_run_strip_peer(const vip_abf* f, const uint8_t* d_src, const vip_halo* halo, uint8_t* d_dst,
+                           const vip_strip* strip, void* stream) {
+    if (!f || !strip || !halo) return VIP_E_NULL;
+    return run_stencil(f->T, vip::kABF, d_src, nullptr, d_dst, *strip, stream, halo);
 }
 int vip_abf_halo_rows(const vip_abf* f) { return f ? f->T.radius : VIP_E_NULL; }
 
@@ -474,7 +517,7 @@ static int btf_create_rows(vip_btf** out, int width, int height, int ksize, int 
     if (rc == VIP_OK) {
         if ((e = f->ping.alloc(n * 3)) == cudaSuccess && (e = f->pong.alloc(n * 3)) == cudaSuccess &&
             (e = f->guide.alloc(n * 3)) == cudaSuccess && (e = f->blurred.alloc(n * 12)) == cudaSuccess &&
-            (e = f->magnitude.alloc(n * 4)) == cudaSuccess && (e = f->rtv.alloc(n * 4)) == cudaSuccess) {
+            (e = f->rtv.alloc(n * 4)) == cudaSuccess) {
         }
         rc = cu(e);
     }
@@ -501,7 +544,7 @@ int vip_btf_destroy(vip_btf* f) {
 }
 size_t vip_btf_scratch_bytes(const vip_btf* f) {
     if (!f) return 0;
-    return f->ping.bytes + f->pong.bytes + f->guide.bytes + f->blurred.bytes + f->magnitude.bytes + f->rtv.bytes;
+    return f->ping.bytes + f->pong.bytes + f->guide.bytes + f->blurred.bytes + f->rtv.bytes;
 }
 int vip_btf_halo_rows_per_iteration(const vip_btf* f) {
     if (!f) return VIP_E_NULL;
@@ -531,17 +574,13 @@ int vip_btf_iterate_strip(vip_btf* f, const uint8_t* d_src_n, uint8_t* d_dst_n, 
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int g0 = std::max(0, s->out_y0 - R), g1 = std::min(H, s->out_y0 + s->out_rows + R);  // guide rows
     const int b0 = std::max(0, g0 - r), b1 = std::min(H, g1 + r);                              // blurred / rtv rows
-    const int m0 = std::max(0, b0 - r), m1 = std::min(H, b1 + r);                              // magnitude rows
     const int base = s->src_y0;
-    float* mag = static_cast<float*>(f->magnitude.p);
     float* bl = static_cast<float*>(f->blurred.p);
     float* rt = static_cast<float*>(f->rtv.p);
     uint8_t* gd = static_cast<uint8_t*>(f->guide.p);
     cudaError_t e;
-    // the gradient stage (:207) is fused into blur / mRTV: magnitude == nullptr computes it from the image tile
-    (void)mag;
-    (void)m0;
-    (void)m1;
+    // the gradient stage (:207) is fused into blur / mRTV: magnitude == nullptr computes it from the image tile, so the
+    // magnitude image (rows [b0 - r, b1 + r)) is never materialised
     if ((e = vip::launch_blur_rtv(d_src_n, nullptr, bl, rt, W, H, k, base, s->src_rows, base, b0, b1 - b0, st)) !=
         cudaSuccess)
         return cu(e);
@@ -559,10 +598,19 @@ int vip_btf_run(vip_btf* f, const uint8_t* d_src, uint8_t* d_dst, void* stream) 
     const vip_strip s = whole(f->height);
     const uint8_t* in = d_src;
     for (int it = 0; it < f->nitr; it++) {
-        // ping-pong instead of the reference's nitr+2 device-to-device copies; the last iterate lands in d_dst
+        // ping-pong instead of the reference's nitr+2 device-to-device copies; the last iterate lands in d_dst --
+        // unless it would be written while the same pass still reads it (in-place call with one iteration: the
+        // reference works in place because it copies src into its own buffers first, :203-213), then it goes through
+        // the scratch image and one copy
         uint8_t* outp = (it == f->nitr - 1) ? d_dst : static_cast<uint8_t*>((it & 1) ? f->pong.p : f->ping.p);
+        const bool alias = (outp == in);
+        if (alias) outp = static_cast<uint8_t*>(f->ping.p);
         const int rc = vip_btf_iterate_strip(f, in, outp, &s, stream);
         if (rc != VIP_OK) return rc;
+        if (alias) {
+            const cudaError_t e = cudaMemcpyAsync(d_dst, outp, bytes, cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream));
+            if (e != cudaSuccess) return cu(e);
+        }
         in = outp;
     }
     return VIP_OK;

@@ -408,7 +408,10 @@ __device__ __noinline__ void fill_tables_call(const float* __restrict__ lut, con
     fill_tables<LK>(lut, lut_n, w_rows, hw, k, lut_s, w_s, hw_s, n_w);
 }
 
-template <int MODE, int P, int LK>
+// PEER: halo rows that the strip buffer does not hold are staged straight from the neighbouring ranks' device memory
+// (StencilArgs::above / below: peer or IPC-mapped pointers, i.e. NVLink loads inside the tile staging) -- the halo
+// exchange of a row-strip split fused into the filter, no halo copy and no halo rows in the local buffer at all.
+template <int MODE, int P, int LK, bool PEER>
 __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
     stencil_kernel(const StencilArgs a, const int tiles_x, const int n_tiles) {
     using E = typename Elem<MODE>::type;
@@ -466,9 +469,19 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
         const int X0 = tile_x * (kWarps * P);
         const int Y0 = a.out_y0 + tile_y * kTileRows;
 
-        // clamp to the image, then (rows no valid output depends on) to the rows the buffers hold
-        auto buffer_row = [&](const int ey) {
-            return clampi(clampi(Y0 - radius + ey, 0, H - 1), a.src_y0, a.src_y0 + a.src_rows - 1) - a.src_y0;
+        // clamp to the image, then (rows no valid output depends on) to the rows the buffers hold; byte offset of the
+        // row inside a.src / a.guide -- or, for a PEER launch, relative to a.src although the row lives in a neighbour's
+        // buffer (all three are device pointers of one address space, the difference is just an integer)
+        auto row_offset = [&](const int ey) -> long long {
+            const int y = clampi(Y0 - radius + ey, 0, H - 1);
+            const long long pitch = static_cast<long long>(W) * 3;
+            if constexpr (PEER) {
+                if (y < a.src_y0 && a.above)
+                    return (a.above - a.src) + (clampi(y, a.above_y0, a.above_y0 + a.above_rows - 1) - a.above_y0) * pitch;
+                if (y >= a.src_y0 + a.src_rows && a.below)
+                    return (a.below - a.src) + (clampi(y, a.below_y0, a.below_y0 + a.below_rows - 1) - a.below_y0) * pitch;
+            }
+            return (clampi(y, a.src_y0, a.src_y0 + a.src_rows - 1) - a.src_y0) * pitch;
         };
         // Tiles whose columns (plus one spare pixel to the right, which the 4th word of load_packed4 may touch) lie
         // inside the image are staged 4 pixels at a time from aligned 32-bit loads; border tiles and the tw % 4
@@ -479,7 +492,7 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
             const int gpr = tw >> 2;
             for (int item = tid; item < th * gpr; item += kThreads) {
                 const int ey = item / gpr, g = item - ey * gpr;
-                const size_t o = (static_cast<size_t>(buffer_row(ey)) * W + (X0 - radius + 4 * g)) * 3;
+                const long long o = row_offset(ey) + (X0 - radius + 4 * g) * 3;
                 std::uint32_t v[4];
                 load_packed4(a.src + o, v);
                 E* const trow = tile + ey * tp + 4 * g;
@@ -499,7 +512,7 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
             for (int item = tid; item < th * rem; item += kThreads) {
                 const int ey = item / rem, ex = vec_cols + (item - ey * rem);
                 const int gx = clampi(X0 - radius + ex, 0, W - 1);
-                const size_t o = (static_cast<size_t>(buffer_row(ey)) * W + gx) * 3;
+                const long long o = row_offset(ey) + gx * 3;
                 if constexpr (MODE == kJBF) {
                     tile[ey * tp + ex] = make_uint2(load_packed(a.guide + o), load_packed(a.src + o));
                 } else {
@@ -670,15 +683,26 @@ __global__ void stencil_generic_kernel(const StencilArgs a, const int lut_len) {
     if (x >= a.width || y >= a.out_y0 + a.out_rows) return;
     const int W = a.width, H = a.height, r = a.radius, k = 2 * r + 1;
     const std::uint8_t* range = (MODE == kJBF) ? a.guide : a.src;
+    // byte offset (relative to a.src / a.guide) of clamped image row yc; peer halo rows as in the tiled kernels
+    auto row_off = [&](const int yc) -> long long {
+        const long long pitch = static_cast<long long>(W) * 3;
+        if (MODE != kJBF) {
+            if (yc < a.src_y0 && a.above)
+                return (a.above - a.src) + (clampi(yc, a.above_y0, a.above_y0 + a.above_rows - 1) - a.above_y0) * pitch;
+            if (yc >= a.src_y0 + a.src_rows && a.below)
+                return (a.below - a.src) + (clampi(yc, a.below_y0, a.below_y0 + a.below_rows - 1) - a.below_y0) * pitch;
+        }
+        return (clampi(yc, a.src_y0, a.src_y0 + a.src_rows - 1) - a.src_y0) * pitch;
+    };
     const std::uint8_t* cp = range + (static_cast<size_t>(y - a.src_y0) * W + x) * 3;
     const int c0 = cp[0], c1 = cp[1], c2 = cp[2];
     float off0 = 0.f, off1 = 0.f, off2 = 0.f;
     if (MODE == kABF) {
         int b0 = 0, b1 = 0, b2 = 0;
         for (int ky = -r; ky <= r; ++ky) {
-            const int yy = clampi(y + ky, 0, H - 1) - a.src_y0;
+            const long long yo = row_off(clampi(y + ky, 0, H - 1));
             for (int kx = -r; kx <= r; ++kx) {
-                const std::uint8_t* p = a.src + (static_cast<size_t>(yy) * W + clampi(x + kx, 0, W - 1)) * 3;
+                const std::uint8_t* p = a.src + yo + clampi(x + kx, 0, W - 1) * 3;
                 b0 += p[0];
                 b1 += p[1];
                 b2 += p[2];
@@ -691,11 +715,11 @@ __global__ void stencil_generic_kernel(const StencilArgs a, const int lut_len) {
     }
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, sk = 0.f;
     for (int ky = -r; ky <= r; ++ky) {
-        const int yy = clampi(y + ky, 0, H - 1) - a.src_y0;
+        const long long yo = row_off(clampi(y + ky, 0, H - 1));
         for (int kx = -r; kx <= r; ++kx) {
             const float ks = __ldg(a.ks_full + (ky + r) * k + (kx + r));
             if (ks == 0.f) continue;  // masked corner: the reference adds +0.0f
-            const size_t o = (static_cast<size_t>(yy) * W + clampi(x + kx, 0, W - 1)) * 3;
+            const long long o = yo + clampi(x + kx, 0, W - 1) * 3;
             const std::uint8_t* g = range + o;
             const std::uint8_t* p = a.src + o;
             int idx;
@@ -732,13 +756,16 @@ int groups_that_fit(int mode, int radius, int lut_n, int lut_kind) {
     return 0;
 }
 
-template <int MODE, int LK>
+template <int MODE, int LK, bool PEER = false>
 cudaError_t launch_tiled(const StencilArgs& a, int sm_count, cudaStream_t stream) {
     constexpr int P = outputs_per_thread(MODE);
+    if constexpr (!PEER && MODE != kJBF) {
+        if (a.above || a.below) return launch_tiled<MODE, LK, true>(a, sm_count, stream);
+    }
     const int n_groups = groups_that_fit(MODE, a.radius, a.lut_n, LK);
     if (n_groups < 1) return cudaErrorInvalidConfiguration;  // stencil_pick_lut never hands out such a table
     const SmemLayout L = make_layout(MODE, P, a.radius, a.lut_n, LK, n_groups);
-    auto kern = stencil_kernel<MODE, P, LK>;
+    auto kern = stencil_kernel<MODE, P, LK, PEER>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total);
     if (e != cudaSuccess) return e;
     const int tiles_x = (a.width + kWarps * P - 1) / (kWarps * P);

@@ -65,6 +65,11 @@ struct StencilArgs {
     const int* hw;              // device: 2r+1 half widths, hw[ky+r] = floor(sqrt(r^2-ky^2))
     const float* ks_full;       // device: ksize*ksize spatial kernel (the generic large-radius kernel reads it)
     const float* w_rows;        // device: ksize rows of stencil_w_pitch(radius) floats: row ky = its 2*hw+1 non-zero weights from index 0, zero padded
+    // Peer halos (BF / ABF, *_strip_peer entry points): rows above src_y0 / from src_y0 + src_rows on are read straight
+    // from the neighbouring ranks' buffers (peer / IPC-mapped device pointers, NVLink loads) -- nullptr: clamp into src.
+    const std::uint8_t* above;  // holds rows [above_y0, above_y0 + above_rows)
+    const std::uint8_t* below;  // holds rows [below_y0, below_y0 + below_rows)
+    int above_y0, above_rows, below_y0, below_rows;
 };
 
 cudaError_t launch_stencil(StencilMode mode, const StencilArgs& a, int sm_count, cudaStream_t stream);

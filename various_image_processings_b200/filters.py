@@ -11,7 +11,7 @@ import ctypes as C
 import numpy as np
 
 from . import capi
-from .capi import Strip, check, lib
+from .capi import Halo, Strip, check, lib
 
 
 def _ptr(x):
@@ -87,6 +87,25 @@ class DeviceImage:
             check(lib().vip_image_download_async(self._h, out.ctypes.data, _stream(stream)), "vip_image_download_async")
         return out
 
+    def upload_rows(self, host_rows, row0, rows, stream=None):
+        """Rows [row0, row0+rows) of the buffer from a packed host array (pinned for real overlap); asynchronous."""
+        a = host_rows if isinstance(host_rows, np.ndarray) else np.asarray(host_rows)
+        if a.dtype != self.dtype or not a.flags.c_contiguous or a.size != rows * self.width * self.channels:
+            raise ValueError("upload_rows: bad host array")
+        check(lib().vip_image_upload_rows_async(self._h, a.ctypes.data, row0, rows, _stream(stream)),
+              "vip_image_upload_rows_async")
+
+    def download_rows(self, out, row0, rows, stream=None):
+        if out.dtype != self.dtype or not out.flags.c_contiguous or out.size != rows * self.width * self.channels:
+            raise ValueError("download_rows: bad output array")
+        check(lib().vip_image_download_rows_async(self._h, out.ctypes.data, row0, rows, _stream(stream)),
+              "vip_image_download_rows_async")
+        return out
+
+    def row_ptr(self, row):
+        """Device address of row `row` of the buffer."""
+        return self.get() + row * self.width * self.channels * self.dtype.itemsize
+
     def get(self):
         return lib().vip_image_data(self._h)
 
@@ -142,6 +161,11 @@ class CudaBilateralFilter:
         check(lib().vip_bf_run_strip(self._h, _ptr(d_src), _ptr(d_dst), C.byref(strip), _stream(stream)),
               "vip_bf_run_strip")
 
+    def bilateral_filter_strip_peer(self, d_src, halo, d_dst, strip, stream=None):
+        """Strip whose halo rows are staged from the neighbouring ranks' device memory (struct vip_halo)."""
+        check(lib().vip_bf_run_strip_peer(self._h, _ptr(d_src), C.byref(halo), _ptr(d_dst), C.byref(strip), _stream(stream)),
+              "vip_bf_run_strip_peer")
+
     def joint_bilateral_filter_strip(self, d_src, d_guide, d_dst, strip, stream=None):
         check(lib().vip_jbf_run_strip(self._h, _ptr(d_src), _ptr(d_guide), _ptr(d_dst), C.byref(strip), _stream(stream)),
               "vip_jbf_run_strip")
@@ -181,6 +205,10 @@ class CudaAdaptiveBilateralFilter:
     def execute_strip(self, d_src, d_dst, strip, stream=None):
         check(lib().vip_abf_run_strip(self._h, _ptr(d_src), _ptr(d_dst), C.byref(strip), _stream(stream)),
               "vip_abf_run_strip")
+
+    def execute_strip_peer(self, d_src, halo, d_dst, strip, stream=None):
+        check(lib().vip_abf_run_strip_peer(self._h, _ptr(d_src), C.byref(halo), _ptr(d_dst), C.byref(strip), _stream(stream)),
+              "vip_abf_run_strip_peer")
 
     def halo_rows(self):
         return lib().vip_abf_halo_rows(self._h)
@@ -372,3 +400,85 @@ class MultiGpuFilter:
         check(lib().vip_mg_run_batch_host(self._h, h_src.ctypes.data, h_dst.ctypes.data, n_frames),
               "vip_mg_run_batch_host")
         return h_dst
+
+
+# ---------------------------------------------------------------- one process per GPU: IPC memory + neighbour links
+def ipc_export(d_ptr):
+    """64-byte CUDA IPC handle (bytes) of a device allocation's BASE pointer (a DeviceImage, or a raw cudaMalloc pointer)."""
+    h = (C.c_ubyte * capi.VIP_IPC_HANDLE_BYTES)()
+    check(lib().vip_ipc_export(_ptr(d_ptr), h), "vip_ipc_export")
+    return bytes(h)
+
+
+def ipc_open(handle):
+    """Device pointer (int) of another process's allocation; VipError(VIP_E_DEVICE) when there is no peer path."""
+    p = C.c_void_p()
+    buf = (C.c_ubyte * capi.VIP_IPC_HANDLE_BYTES).from_buffer_copy(handle)
+    check(lib().vip_ipc_open(buf, C.byref(p)), "vip_ipc_open")
+    return p.value
+
+
+def ipc_close(ptr):
+    check(lib().vip_ipc_close(ptr), "vip_ipc_close")
+
+
+def copy_rows(d_dst, dst_y0, d_src, src_y0, y0, rows, width, stream=None):
+    """Rows [y0, y0+rows) of a packed BGR image from one strip buffer into another (the explicit halo pull; P2P over NVLink
+    when the two pointers live on different devices)."""
+    check(lib().vip_copy_rows(_ptr(d_dst), dst_y0, _ptr(d_src), src_y0, y0, rows, width, _stream(stream)), "vip_copy_rows")
+
+
+def make_halo(above=None, below=None):
+    """struct vip_halo from (ptr, y0, rows) tuples (None at the image border)."""
+    h = Halo()
+    if above is not None:
+        h.d_above, h.above_y0, h.above_rows = _ptr(above[0]), above[1], above[2]
+    if below is not None:
+        h.d_below, h.below_y0, h.below_rows = _ptr(below[0]), below[1], below[2]
+    return h
+
+
+class StripLink:
+    """vip_link: stream-ordered "ready" / "consumed" step counters between a rank and its two strip neighbours, stored
+    into the neighbour's flag block over NVLink -- no host synchronisation inside a frame pipeline."""
+
+    def __init__(self, n_slots):
+        self._h = C.c_void_p()
+        check(lib().vip_link_create(C.byref(self._h), n_slots), "vip_link_create")
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            if capi is not None:
+                capi.release('vip_link_destroy', h)
+
+    def export(self):
+        h = (C.c_ubyte * capi.VIP_IPC_HANDLE_BYTES)()
+        check(lib().vip_link_export(self._h, h), "vip_link_export")
+        return bytes(h)
+
+    def connect(self, above_handle, below_handle):
+        mk = lambda b: (C.c_ubyte * capi.VIP_IPC_HANDLE_BYTES).from_buffer_copy(b) if b is not None else None
+        check(lib().vip_link_connect(self._h, mk(above_handle), mk(below_handle)), "vip_link_connect")
+
+    def connect_local(self, above, below):
+        check(lib().vip_link_connect_local(self._h, above._h if above else None, below._h if below else None),
+              "vip_link_connect_local")
+
+    def set_timeout_ms(self, ms):
+        check(lib().vip_link_set_timeout_ms(self._h, ms), "vip_link_set_timeout_ms")
+
+    def signal_ready(self, slot, step, stream=None):
+        check(lib().vip_link_signal_ready(self._h, slot, step, _stream(stream)), "vip_link_signal_ready")
+
+    def wait_ready(self, slot, step, stream=None):
+        check(lib().vip_link_wait_ready(self._h, slot, step, _stream(stream)), "vip_link_wait_ready")
+
+    def signal_consumed(self, slot, step, stream=None):
+        check(lib().vip_link_signal_consumed(self._h, slot, step, _stream(stream)), "vip_link_signal_consumed")
+
+    def wait_consumed(self, slot, step, stream=None):
+        check(lib().vip_link_wait_consumed(self._h, slot, step, _stream(stream)), "vip_link_wait_consumed")
+
+    def status(self):
+        check(lib().vip_link_status(self._h), "vip_link_status")
