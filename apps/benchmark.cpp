@@ -190,6 +190,12 @@ int main(int argc, char** argv) {
                            device_ms([&] { filter.execute_async(d_input_image->get(), d_dst.get(), nullptr); })});
     }
 
+    // the reference's harness ends with a CPU-only SuperpixelSLIC section (sample/benchmark/main.cpp:188-201, 240).  SLIC
+    // (and Wexler inpainting) are plain compute that COULD be CUDA kernels; they are outside the edge-preserving-filter hot
+    // path this library covers and are not built -- said here instead of silently dropping the section
+    std::cout << "superpixel SLIC [cuda] : not implemented (outside the hot-path scope of this library; no CUDA twin in the reference either)"
+              << std::endl;
+
     if (device_time)
         for (const auto& r : results) print_duration(r.name + " [cuda, async x" + std::to_string(n) + "]", r.device_ms);
     if (json) {

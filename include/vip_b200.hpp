@@ -200,6 +200,10 @@ public:
     bool ok() const { return handle_ != nullptr; }
     void execute(const std::uint8_t* h_src, std::uint8_t* h_dst);  // scatter, run, gather
     void execute_batch(const std::uint8_t* h_src, std::uint8_t* h_dst, int n_frames);
+    // every frame through a set of filters (VIP_MG_SET_BF | VIP_MG_SET_ABF | VIP_MG_SET_BTF), one upload per frame;
+    // h_dst[j] receives filter j of the set (entries of filters not in the set may be null)
+    void execute_batch_set(int filter_set, const std::uint8_t* h_src, std::uint8_t* const h_dst[3], int n_frames);
+    bool peer_access() const;   // halo rows move GPU<->GPU with peer access enabled (false: staged through the host)
     float last_run_ms() const;
 
 private:

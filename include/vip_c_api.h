@@ -261,6 +261,9 @@ VIP_API int vip_mg_create(vip_mg** out, const int* device_ids, int n_devices, in
  * results are bit-identical either way. */
 #define VIP_MG_FLAG_BTF_EXCHANGE 1
 #define VIP_MG_FLAG_BTF_DEEP_HALO 2
+/* Fail with VIP_E_DEVICE when two neighbouring slots sit on different devices without peer access (by default
+ * cudaMemcpyPeerAsync then stages the halo rows through the host; vip_mg_peer_access() reports which one a handle uses) */
+#define VIP_MG_FLAG_REQUIRE_P2P 4
 VIP_API int vip_mg_create_ex(vip_mg** out, const int* device_ids, int n_devices, int kind, int width, int height,
                              int ksize, float sigma_space, float sigma_color, int nitr, int flags);
 VIP_API int vip_mg_destroy(vip_mg* m);
@@ -289,9 +292,21 @@ VIP_API int vip_mg_wait(vip_mg* m);
 VIP_API int vip_mg_gather_host(vip_mg* m, uint8_t* h_dst);
 /* Device time of the last run, max over devices, from CUDA events (ms). */
 VIP_API int vip_mg_last_run_ms(const vip_mg* m, float* ms);
-/* Independent frames: frame f goes to device slot f % n.  h_src/h_dst hold n_frames packed images (pinned memory
- * recommended).  Uploads, kernels and downloads of different frames overlap on two streams per device. */
+/* Independent frames: frame f goes to device slot f % n.  h_src/h_dst hold n_frames packed images.  Uploads, kernels
+ * and downloads of different frames overlap on two streams per device -- when the host memory is PINNED (vip_host_alloc
+ * or cudaHostRegister); with pageable memory the copies serialise.  One enqueueing host thread per device. */
 VIP_API int vip_mg_run_batch_host(vip_mg* m, const uint8_t* h_src, uint8_t* h_dst, int n_frames);
+/* The same through a SET of filters (BASELINE configs[4]: every frame through all three): each frame is uploaded once,
+ * filter j of the set writes h_dst[j] (entries of filters not in the set may be NULL).  The filters share the handle's
+ * ksize / sigmas / nitr; whatever its own kind, the missing filter objects are created on first use. */
+#define VIP_MG_SET_BF 1
+#define VIP_MG_SET_ABF 2
+#define VIP_MG_SET_BTF 4
+VIP_API int vip_mg_run_batch_set_host(vip_mg* m, int filter_set, const uint8_t* h_src, uint8_t* const* h_dst /* [3] */,
+                                      int n_frames);
+/* 1: every pair of neighbouring slots on different devices has peer access enabled (halo rows move GPU<->GPU over
+ * NVLink); 0: at least one pair stages through the host. */
+VIP_API int vip_mg_peer_access(const vip_mg* m);
 
 /* ---- one process per GPU: cross-process device memory and neighbour ordering (csrc/link.cu) -------------------
  * Under torchrun every rank owns one GPU and one row strip.  vip_ipc_export() turns a device allocation (the base

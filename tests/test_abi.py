@@ -101,6 +101,21 @@ def test_cpp_dropin_headers_compile_without_cuda(tmp_path):
     assert so.exists()
 
 
+def test_impl_surface_of_the_reference_tests_compiles(tmp_path):
+    """The reference's tests include "<name>_impl.cuh", subclass the public classes and call impl_->... with
+    thrust::device_vector arguments (test/bilateral_texture_filter.cu:115-136).  The same pattern builds against this
+    library with include/cuda/impl on the include path in place of the reference's src/ (nvcc cross-compiles here)."""
+    import shutil
+    if shutil.which("nvcc") is None:
+        pytest.skip("nvcc not on PATH")
+    so = tmp_path / "libpattern.so"
+    subprocess.check_call(["nvcc", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC",
+                           "-I", os.path.join(ROOT, "include"), "-I", os.path.join(ROOT, "include", "cuda", "impl"),
+                           os.path.join(ROOT, "tests", "impl_surface_pattern.cu"), "-o", str(so),
+                           "-L", os.path.dirname(capi.LIB_PATH), "-lvip_b200"])
+    assert so.exists()
+
+
 def test_division_by_constant_shortcut_is_exact(tmp_path):
     """csrc/btf.cu replaces __fdiv_rn(x, K*K) and __fdiv_rn(x, 3.f) by a 3-instruction sequence; exhaustive proof."""
     exe = tmp_path / "div_const_check"

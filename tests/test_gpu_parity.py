@@ -893,3 +893,55 @@ def test_btf_vs_reference_cpu_report(vip, content):
     r = rep.compare(vip, content, 3840, 512)
     any_share, gt1_share = BTF_O1_BOUNDS[content]
     assert r["share_gt0"] <= any_share and r["share_gt1"] <= gt1_share, r
+
+
+def test_multigpu_batch_filter_set(vip):
+    """configs[4]: every frame through all three filters -- one upload per frame, one enqueueing thread per device."""
+    w, h, nf, k = 96, 80, 7, 9
+    frames = np.stack([O.rand_image(w, h, seed=300 + f) for f in range(nf)])
+    outs = {name: np.zeros_like(frames) for name in ("bf", "abf", "btf")}
+    n = torch.cuda.device_count()
+    mg = vip.MultiGpuFilter([i % n for i in range(3)], "abf", w, h, ksize=k, nitr=2)
+    mg.execute_batch_set(frames, outs, nf)
+    for f in range(nf):
+        assert np.array_equal(outs["bf"][f], O.o_bf(frames[f], k))
+        assert np.array_equal(outs["abf"][f], O.o_abf(frames[f], k))
+        assert np.array_equal(outs["btf"][f], O.o_btf(frames[f], k, 2))
+    only = {"btf": np.zeros_like(frames)}
+    mg.execute_batch_set(frames, only, nf, filters=("btf",))       # a subset, same handle
+    assert np.array_equal(only["btf"], outs["btf"])
+    assert mg.peer_access() in (True, False)
+
+
+def test_multigpu_btf_exchange_back_to_back_runs(vip):
+    """Two runs without a gather in between (the advisor's write-after-read case of the exchange mode with an even
+    iteration count): the second run's first iteration may only overwrite a ping buffer once the neighbours' last halo
+    pulls of the first run are complete."""
+    w, h, k, nitr, n = 128, 4 * 60, 9, 4, 4
+    img = O.smooth_image(w, h, seed=77)
+    nd = torch.cuda.device_count()
+    mg = vip.MultiGpuFilter([i % nd for i in range(n)], "btf", w, h, ksize=k, nitr=nitr, btf_halo="exchange")
+    mg.scatter_host(img)
+    for _ in range(4):
+        mg.run_async()
+    out = np.empty_like(img)
+    mg.gather_host(out)
+    assert np.array_equal(out, run_btf(vip, img, k, nitr))
+
+
+def test_multigpu_require_p2p_flag(vip):
+    """Same device listed twice: no peer pair at all, so the flag is satisfied and the transport reads as P2P-clean."""
+    mg = vip.MultiGpuFilter([0, 0], "bf", 64, 64, ksize=5, require_p2p=True)
+    assert mg.peer_access() is True
+
+
+def test_btf_in_place_single_iteration(vip):
+    """d_src == d_dst with one iteration: the reference copies src into its own buffers first, so in-place works there."""
+    w, h = 96, 72
+    img = O.smooth_image(w, h, seed=9)
+    d = dev(img)
+    vip.CudaBilateralTextureFilter(w, h, 9, 1).execute(d, d)
+    assert np.array_equal(d.cpu().numpy(), O.o_btf(img, 9, 1))
+    d = dev(img)
+    vip.CudaBilateralTextureFilter(w, h, 9, 2).execute(d, d)
+    assert np.array_equal(d.cpu().numpy(), O.o_btf(img, 9, 2))

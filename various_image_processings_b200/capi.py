@@ -16,7 +16,8 @@ VIP_OK = 0
  VIP_E_DEVICE) = range(-1, -9, -1)
 VIP_LUT_CUDA, VIP_LUT_CPU = 0, 1
 VIP_MG_BF, VIP_MG_ABF, VIP_MG_BTF = 0, 1, 2
-VIP_MG_FLAG_BTF_EXCHANGE, VIP_MG_FLAG_BTF_DEEP_HALO = 1, 2
+VIP_MG_FLAG_BTF_EXCHANGE, VIP_MG_FLAG_BTF_DEEP_HALO, VIP_MG_FLAG_REQUIRE_P2P = 1, 2, 4
+VIP_MG_SET_BF, VIP_MG_SET_ABF, VIP_MG_SET_BTF = 1, 2, 4
 VIP_SRC_U8, VIP_SRC_U16, VIP_SRC_F32 = 0, 1, 2
 VIP_IPC_HANDLE_BYTES = 64
 
@@ -123,6 +124,8 @@ SIGNATURES = {
     "vip_mg_gather_host": (_i, [_vp, _vp]),
     "vip_mg_last_run_ms": (_i, [_vp, C.POINTER(C.c_float)]),
     "vip_mg_run_batch_host": (_i, [_vp, _vp, _vp, _i]),
+    "vip_mg_run_batch_set_host": (_i, [_vp, _i, _vp, C.POINTER(C.c_void_p), _i]),
+    "vip_mg_peer_access": (_i, [_vp]),
     "vip_ipc_export": (_i, [_vp, _vp]),
     "vip_ipc_open": (_i, [_vp, _pp]),
     "vip_ipc_close": (_i, [_vp]),

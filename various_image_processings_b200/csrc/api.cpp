@@ -5,13 +5,11 @@
 #include <utility>
 
 #include "../../include/vip_b200.hpp"
-
-namespace {
-inline void report(int status, const char* what, const char* file, int line) {
-    if (status != VIP_OK) std::fprintf(stderr, "vip_b200: %s failed: %s (%d) at %s:%d\n", what, vip_status_string(status), status, file, line);
-}
-}  // namespace
-#define VIP_CHECK(expr) report((expr), #expr, __FILE__, __LINE__)
+// the Impl classes are public headers (include/cuda/impl/*.cuh) with the reference's member names, so that code written
+// against the reference's src/*_impl.cuh -- its own tests -- compiles against this library too
+#include "../../include/cuda/impl/adaptive_bilateral_filter_impl.cuh"
+#include "../../include/cuda/impl/bilateral_filter_impl.cuh"
+#include "../../include/cuda/impl/bilateral_texture_filter_impl.cuh"
 
 // ---------------------------------------------------------------- DeviceImage
 template <typename T>
@@ -65,20 +63,6 @@ template class VIP_API DeviceImage<std::uint8_t>;
 template class VIP_API DeviceImage<float>;
 
 // ---------------------------------------------------------------- CudaBilateralFilter
-class CudaBilateralFilter::Impl {
-public:
-    Impl(int w, int h, int ksize, float ss, float sc) { VIP_CHECK(vip_bf_create(&handle, w, h, ksize, ss, sc)); }
-    ~Impl() { vip_bf_destroy(handle); }
-    // same member names as the reference's Impl (src/bilateral_filter_impl.cuh:17-25): launch, no sync
-    void bilateral_filter(const std::uint8_t* d_src, std::uint8_t* d_dst, void* stream = nullptr) const {
-        VIP_CHECK(vip_bf_run(handle, d_src, d_dst, stream));
-    }
-    void joint_bilateral_filter(const std::uint8_t* d_src, const std::uint8_t* d_guide, std::uint8_t* d_dst,
-                                void* stream = nullptr) const {
-        VIP_CHECK(vip_jbf_run(handle, d_src, d_guide, d_dst, stream));
-    }
-    vip_bf* handle = nullptr;
-};
 
 CudaBilateralFilter::CudaBilateralFilter(const int width, const int height, const int ksize, const float sigma_space,
                                          const float sigma_color)
@@ -107,15 +91,6 @@ void CudaBilateralFilter::bilateral_filter_strip(const std::uint8_t* d_src, std:
 int CudaBilateralFilter::halo_rows() const { return vip_bf_halo_rows(impl_->handle); }
 
 // ---------------------------------------------------------------- CudaAdaptiveBilateralFilter
-class CudaAdaptiveBilateralFilter::Impl {
-public:
-    Impl(int w, int h, int ksize, float ss, float sc) { VIP_CHECK(vip_abf_create(&handle, w, h, ksize, ss, sc)); }
-    ~Impl() { vip_abf_destroy(handle); }
-    void execute(const std::uint8_t* d_src, std::uint8_t* d_dst, void* stream = nullptr) const {
-        VIP_CHECK(vip_abf_run(handle, d_src, d_dst, stream));
-    }
-    vip_abf* handle = nullptr;
-};
 
 CudaAdaptiveBilateralFilter::CudaAdaptiveBilateralFilter(const int width, const int height, const int ksize,
                                                          const float sigma_space, const float sigma_color)
@@ -135,23 +110,6 @@ void CudaAdaptiveBilateralFilter::execute_strip(const std::uint8_t* d_src, std::
 int CudaAdaptiveBilateralFilter::halo_rows() const { return vip_abf_halo_rows(impl_->handle); }
 
 // ---------------------------------------------------------------- CudaBilateralTextureFilter
-class CudaBilateralTextureFilter::Impl {
-public:
-    Impl(int w, int h, int ksize, int nitr) { VIP_CHECK(vip_btf_create(&handle, w, h, ksize, nitr)); }
-    ~Impl() { vip_btf_destroy(handle); }
-    void execute(const std::uint8_t* d_src, std::uint8_t* d_dst, void* stream = nullptr) {
-        VIP_CHECK(vip_btf_run(handle, d_src, d_dst, stream));
-    }
-    // stage entry points of the reference's Impl (src/bilateral_texture_filter_impl.cuh:19-28), on raw device pointers
-    void compute_blur_and_rtv(const std::uint8_t* d_image, const float* d_magnitude, float* d_blurred, float* d_rtv,
-                              void* stream = nullptr) {
-        VIP_CHECK(vip_btf_blur_rtv(handle, d_image, d_magnitude, d_blurred, d_rtv, stream));
-    }
-    void compute_guide(const float* d_blurred, const float* d_rtv, std::uint8_t* d_guide, void* stream = nullptr) {
-        VIP_CHECK(vip_btf_guide(handle, d_blurred, d_rtv, d_guide, stream));
-    }
-    vip_btf* handle = nullptr;
-};
 
 CudaBilateralTextureFilter::CudaBilateralTextureFilter(const int width, const int height, const int ksize,
                                                        const int nitr)
@@ -211,6 +169,10 @@ void MultiGpuFilter::execute(const std::uint8_t* h_src, std::uint8_t* h_dst) {
 void MultiGpuFilter::execute_batch(const std::uint8_t* h_src, std::uint8_t* h_dst, int n_frames) {
     VIP_CHECK(vip_mg_run_batch_host(handle_, h_src, h_dst, n_frames));
 }
+void MultiGpuFilter::execute_batch_set(int filter_set, const std::uint8_t* h_src, std::uint8_t* const h_dst[3], int n_frames) {
+    VIP_CHECK(vip_mg_run_batch_set_host(handle_, filter_set, h_src, h_dst, n_frames));
+}
+bool MultiGpuFilter::peer_access() const { return vip_mg_peer_access(handle_) == 1; }
 float MultiGpuFilter::last_run_ms() const {
     float ms = 0.f;
     VIP_CHECK(vip_mg_last_run_ms(handle_, &ms));

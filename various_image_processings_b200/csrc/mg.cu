@@ -50,6 +50,9 @@ struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     std::vector<cudaEvent_t> ev_iter;  // BTF: iterate `it` is complete on this slot
+    cudaEvent_t ev_pulled = nullptr;   // BTF exchange: this slot's last halo pull of a run is complete
+    bool pulled_valid = false;         // ev_pulled has been recorded by the previous run
+    int peer_up = -1, peer_dn = -1;    // transport to the neighbouring slots: 1 P2P enabled, 0 staged through the host, -1 same device / none
     uint8_t* src = nullptr;            // rows [sy0, sy0+srows)
     uint8_t* buf[2] = {nullptr, nullptr};  // BF/ABF: buf[0] = dst (owned rows only); BTF: ping/pong over [sy0, ..)
     vip_bf* bf = nullptr;
@@ -58,7 +61,7 @@ struct Slot {
     // batch mode (whole frames): two in-flight lanes
     cudaStream_t bstream[2] = {nullptr, nullptr};
     uint8_t* bsrc[2] = {nullptr, nullptr};
-    uint8_t* bdst[2] = {nullptr, nullptr};
+    uint8_t* bdst[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};   // per lane: BF / ABF / BTF output
     vip_btf* bbtf[2] = {nullptr, nullptr};
 };
 
@@ -78,7 +81,6 @@ struct vip_mg {
     float ss = 0.f, sc = 0.f;
     int result_buf = 0;  // BTF: which of buf[0/1] holds the final iterate (-1: src)
     bool btf_deep = false;  // BTF: deep-halo mode (no exchange), see the header comment
-    bool batch_ready = false;
     std::vector<Slot> slots;
     std::vector<std::unique_ptr<Worker>> workers;          // one enqueueing thread per slot
     std::unique_ptr<std::atomic<int>[]> iter_recorded;     // BTF: iterations whose "done" event slot i has recorded
@@ -100,12 +102,14 @@ int free_slot(vip_mg* m, Slot& s) {
     for (int i = 0; i < 2; i++) {
         if (s.bbtf[i]) vip_btf_destroy(s.bbtf[i]);
         if (s.bsrc[i]) cudaFree(s.bsrc[i]);
-        if (s.bdst[i]) cudaFree(s.bdst[i]);
+        for (int j = 0; j < 3; j++)
+            if (s.bdst[i][j]) cudaFree(s.bdst[i][j]);
         if (s.bstream[i]) cudaStreamDestroy(s.bstream[i]);
         if (s.buf[i]) cudaFree(s.buf[i]);
     }
     if (s.src) cudaFree(s.src);
     for (cudaEvent_t e : s.ev_iter) cudaEventDestroy(e);
+    if (s.ev_pulled) cudaEventDestroy(s.ev_pulled);
     if (s.ev_start) cudaEventDestroy(s.ev_start);
     if (s.ev_stop) cudaEventDestroy(s.ev_stop);
     if (s.stream) cudaStreamDestroy(s.stream);
@@ -129,6 +133,7 @@ int plan_slot(int n_devices, int slot, int kind, int height, int ksize, int nitr
     if (ksize < 1 || (ksize & 1) == 0) return VIP_E_KSIZE;
     if (kind == VIP_MG_BTF && nitr < 0) return VIP_E_UNSUPPORTED;
     if ((flags & VIP_MG_FLAG_BTF_EXCHANGE) && (flags & VIP_MG_FLAG_BTF_DEEP_HALO)) return VIP_E_UNSUPPORTED;
+    if (flags & ~(VIP_MG_FLAG_BTF_EXCHANGE | VIP_MG_FLAG_BTF_DEEP_HALO | VIP_MG_FLAG_REQUIRE_P2P)) return VIP_E_UNSUPPORTED;
     const int halo = (kind == VIP_MG_BTF) ? (ksize - 1) + 2 * (ksize / 2) + 1 : ksize / 2;
     bool deep = false;
     if (kind == VIP_MG_BTF && n_devices > 1 && nitr > 1) {
@@ -166,6 +171,16 @@ int enqueue_slot(vip_mg* m, int i) {
         auto wait_recorded = [&](int j, int want) {  // the neighbour's event must be RECORDED before it can be waited on
             while (m->iter_recorded[j].load(std::memory_order_acquire) < want) std::this_thread::yield();
         };
+        // Exchange mode, run N+1 after run N without a gather in between: the neighbours' last halo pulls of run N read
+        // this slot's ping / pong buffers; they must be complete before iteration 0 overwrites buf[0].  Their events were
+        // recorded while run N was being enqueued, which vip_mg_run_async has waited for.
+        if (!m->btf_deep) {
+            for (int j = i - 1; j <= i + 1; j += 2) {
+                if (j < 0 || j >= m->n || !m->slots[j].pulled_valid) continue;
+                if ((e = cudaStreamWaitEvent(s.stream, m->slots[j].ev_pulled, 0)) != cudaSuccess) return cu(e);
+            }
+        }
+        bool pulled = false;
         for (int it = 0; it < m->nitr; it++) {
             const int ob = it & 1;
             const uint8_t* in = (it == 0) ? s.src : s.buf[ob ^ 1];
@@ -188,6 +203,7 @@ int enqueue_slot(vip_mg* m, int i) {
                     e = cudaMemcpyPeerAsync(s.buf[ob], s.device, up.buf[ob] + row_bytes * (s.sy0 - up.sy0), up.device,
                                             row_bytes * (s.y0 - s.sy0), s.stream);
                     if (e != cudaSuccess) return cu(e);
+                    pulled = true;
                 }
                 const int below0 = s.y0 + s.rows, below1 = s.sy0 + s.srows;
                 if (i + 1 < m->n && below1 > below0) {
@@ -198,9 +214,14 @@ int enqueue_slot(vip_mg* m, int i) {
                                             dn.buf[ob] + row_bytes * (below0 - dn.sy0), dn.device,
                                             row_bytes * (below1 - below0), s.stream);
                     if (e != cudaSuccess) return cu(e);
+                    pulled = true;
                 }
             }
         }
+        if (pulled) {
+            if ((e = cudaEventRecord(s.ev_pulled, s.stream)) != cudaSuccess) return cu(e);
+        }
+        s.pulled_valid = pulled;
     }
     if ((e = cudaEventRecord(s.ev_stop, s.stream)) != cudaSuccess) return cu(e);
     return VIP_OK;
@@ -308,12 +329,17 @@ int vip_mg_create_ex(vip_mg** out, const int* device_ids, int n_devices, int kin
         // cudaMemcpyPeerAsync then falls back to staging through the host)
         for (int j = i - 1; j <= i + 1; j += 2) {
             if (j < 0 || j >= n_devices || device_ids[j] == s.device) continue;
-            int can = 0;
+            int can = 0, ok = 0;
             if (cudaDeviceCanAccessPeer(&can, s.device, device_ids[j]) == cudaSuccess && can) {
-                cudaDeviceEnablePeerAccess(device_ids[j], 0);
-                cudaGetLastError();
+                const cudaError_t pe = cudaDeviceEnablePeerAccess(device_ids[j], 0);
+                ok = (pe == cudaSuccess || pe == cudaErrorPeerAccessAlreadyEnabled) ? 1 : 0;
             }
+            cudaGetLastError();
+            (j < i ? s.peer_up : s.peer_dn) = ok;
+            // without peer access cudaMemcpyPeerAsync stages through the host: allowed unless the caller asked for P2P
+            if (!ok && (flags & VIP_MG_FLAG_REQUIRE_P2P)) { rc = VIP_E_DEVICE; break; }
         }
+        if (rc != VIP_OK) break;
         if ((e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking)) != cudaSuccess) { rc = cu(e); break; }
         if ((e = cudaEventCreate(&s.ev_start)) != cudaSuccess) { rc = cu(e); break; }
         if ((e = cudaEventCreate(&s.ev_stop)) != cudaSuccess) { rc = cu(e); break; }
@@ -326,6 +352,7 @@ int vip_mg_create_ex(vip_mg** out, const int* device_ids, int n_devices, int kin
             for (auto& ev : s.ev_iter)
                 if ((e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) break;
             if (e != cudaSuccess) { rc = cu(e); break; }
+            if ((e = cudaEventCreateWithFlags(&s.ev_pulled, cudaEventDisableTiming)) != cudaSuccess) { rc = cu(e); break; }
             rc = vip_btf_create_rows_internal(&s.btf, width, height, ksize, nitr, s.srows);
         } else {
             if ((e = cudaMalloc(reinterpret_cast<void**>(&s.buf[0]), row_bytes * s.rows)) != cudaSuccess) { rc = cu(e); break; }
@@ -404,13 +431,13 @@ int vip_mg_scatter_device(vip_mg* m, const uint8_t* d_src_on_dev0) {
 
 int vip_mg_run_async(vip_mg* m) {
     if (!m) return VIP_E_NULL;
-    const int rc = wait_workers(m);  // a previous run still being enqueued
-    if (rc != VIP_OK) return rc;
+    wait_workers(m);  // a previous run still being enqueued (its status was reported by its own wait / gather)
     for (int i = 0; i < m->n; i++) m->iter_recorded[i].store(0, std::memory_order_release);
     if (m->kind == VIP_MG_BTF) m->result_buf = m->nitr > 0 ? ((m->nitr - 1) & 1) : -1;
     for (auto& wp : m->workers) {
         {
             std::lock_guard<std::mutex> lock(wp->mu);
+            wp->rc = VIP_OK;   // a failed run does not poison the handle: every run reports its own status
             wp->cmd_gen++;
         }
         wp->cv.notify_all();
@@ -474,54 +501,98 @@ int vip_mg_last_run_ms(const vip_mg* m, float* ms) {
     return VIP_OK;
 }
 
-int vip_mg_run_batch_host(vip_mg* m, const uint8_t* h_src, uint8_t* h_dst, int n_frames) {
-    if (!m || !h_src || !h_dst) return VIP_E_NULL;
-    if (n_frames < 0) return VIP_E_SIZE;
-    wait_workers(m);
-    DeviceGuard guard;
+// Lazy, idempotent set-up of the frame-batch lanes of one slot for the filters in `set` (a failure leaves what exists
+// in place; the next call continues where this one stopped).
+static int batch_setup_slot(vip_mg* m, Slot& s, int set) {
     const size_t frame_bytes = static_cast<size_t>(m->width) * m->height * 3;
     cudaError_t e;
-    if (!m->batch_ready) {
-        for (Slot& s : m->slots) {
-            if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
-            for (int l = 0; l < 2; l++) {
-                if ((e = cudaStreamCreateWithFlags(&s.bstream[l], cudaStreamNonBlocking)) != cudaSuccess) return cu(e);
-                if ((e = cudaMalloc(reinterpret_cast<void**>(&s.bsrc[l]), frame_bytes)) != cudaSuccess) return cu(e);
-                if ((e = cudaMalloc(reinterpret_cast<void**>(&s.bdst[l]), frame_bytes)) != cudaSuccess) return cu(e);
-                if (m->kind == VIP_MG_BTF) {
-                    const int rc = vip_btf_create(&s.bbtf[l], m->width, m->height, m->ksize, m->nitr);
-                    if (rc != VIP_OK) return rc;
-                }
-            }
+    if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
+    for (int l = 0; l < 2; l++) {
+        if (!s.bstream[l] && (e = cudaStreamCreateWithFlags(&s.bstream[l], cudaStreamNonBlocking)) != cudaSuccess) return cu(e);
+        if (!s.bsrc[l] && (e = cudaMalloc(reinterpret_cast<void**>(&s.bsrc[l]), frame_bytes)) != cudaSuccess) return cu(e);
+        for (int j = 0; j < 3; j++)
+            if ((set >> j & 1) && !s.bdst[l][j] &&
+                (e = cudaMalloc(reinterpret_cast<void**>(&s.bdst[l][j]), frame_bytes)) != cudaSuccess)
+                return cu(e);
+        if ((set & VIP_MG_SET_BTF) && !s.bbtf[l]) {
+            const int rc = vip_btf_create(&s.bbtf[l], m->width, m->height, m->ksize, m->nitr);
+            if (rc != VIP_OK) return rc;
         }
-        m->batch_ready = true;
     }
-    std::vector<int> next_lane(m->n, 0);
-    for (int f = 0; f < n_frames; f++) {
-        const int i = f % m->n;
-        Slot& s = m->slots[i];
-        const int l = next_lane[i];
-        next_lane[i] ^= 1;
-        if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
-        cudaStream_t st = s.bstream[l];
-        if ((e = cudaMemcpyAsync(s.bsrc[l], h_src + frame_bytes * f, frame_bytes, cudaMemcpyHostToDevice, st)) !=
-            cudaSuccess)
-            return cu(e);
-        int rc;
-        if (m->kind == VIP_MG_BF) rc = vip_bf_run(s.bf, s.bsrc[l], s.bdst[l], st);
-        else if (m->kind == VIP_MG_ABF) rc = vip_abf_run(s.abf, s.bsrc[l], s.bdst[l], st);
-        else rc = vip_btf_run(s.bbtf[l], s.bsrc[l], s.bdst[l], st);
+    if ((set & VIP_MG_SET_BF) && !s.bf) {
+        const int rc = vip_bf_create(&s.bf, m->width, m->height, m->ksize, m->ss, m->sc);
         if (rc != VIP_OK) return rc;
-        if ((e = cudaMemcpyAsync(h_dst + frame_bytes * f, s.bdst[l], frame_bytes, cudaMemcpyDeviceToHost, st)) !=
-            cudaSuccess)
-            return cu(e);
     }
-    for (Slot& s : m->slots) {
-        if ((e = cudaSetDevice(s.device)) != cudaSuccess) return cu(e);
-        for (int l = 0; l < 2; l++)
-            if ((e = cudaStreamSynchronize(s.bstream[l])) != cudaSuccess) return cu(e);
+    if ((set & VIP_MG_SET_ABF) && !s.abf) {
+        const int rc = vip_abf_create(&s.abf, m->width, m->height, m->ksize, m->ss, m->sc);
+        if (rc != VIP_OK) return rc;
     }
     return VIP_OK;
+}
+
+// Frames i, i + n, i + 2n, ... on slot i: upload ONCE, every filter of the set, one download per filter; two lanes so
+// that the copies of one frame overlap the kernels of the other.  Runs on its own host thread (one per device).
+static int batch_run_slot(vip_mg* m, int i, int set, const uint8_t* h_src, uint8_t* const* h_dst, int n_frames) {
+    Slot& s = m->slots[i];
+    const size_t frame_bytes = static_cast<size_t>(m->width) * m->height * 3;
+    cudaError_t e;
+    int rc = batch_setup_slot(m, s, set);
+    if (rc != VIP_OK) return rc;
+    int lane = 0;
+    for (int f = i; f < n_frames; f += m->n, lane ^= 1) {
+        cudaStream_t st = s.bstream[lane];
+        if ((e = cudaMemcpyAsync(s.bsrc[lane], h_src + frame_bytes * f, frame_bytes, cudaMemcpyHostToDevice, st)) != cudaSuccess)
+            return cu(e);
+        if (set & VIP_MG_SET_BF)
+            if ((rc = vip_bf_run(s.bf, s.bsrc[lane], s.bdst[lane][0], st)) != VIP_OK) return rc;
+        if (set & VIP_MG_SET_ABF)
+            if ((rc = vip_abf_run(s.abf, s.bsrc[lane], s.bdst[lane][1], st)) != VIP_OK) return rc;
+        if (set & VIP_MG_SET_BTF)
+            if ((rc = vip_btf_run(s.bbtf[lane], s.bsrc[lane], s.bdst[lane][2], st)) != VIP_OK) return rc;
+        for (int j = 0; j < 3; j++)
+            if (set >> j & 1)
+                if ((e = cudaMemcpyAsync(h_dst[j] + frame_bytes * f, s.bdst[lane][j], frame_bytes, cudaMemcpyDeviceToHost, st)) !=
+                    cudaSuccess)
+                    return cu(e);
+    }
+    for (int l = 0; l < 2; l++)
+        if ((e = cudaStreamSynchronize(s.bstream[l])) != cudaSuccess) return cu(e);
+    return VIP_OK;
+}
+
+int vip_mg_run_batch_set_host(vip_mg* m, int filter_set, const uint8_t* h_src, uint8_t* const* h_dst, int n_frames) {
+    if (!m || !h_src || !h_dst) return VIP_E_NULL;
+    if (n_frames < 0) return VIP_E_SIZE;
+    if (filter_set <= 0 || filter_set > 7) return VIP_E_UNSUPPORTED;
+    for (int j = 0; j < 3; j++)
+        if ((filter_set >> j & 1) && !h_dst[j]) return VIP_E_NULL;
+    if ((filter_set & VIP_MG_SET_BTF) && (m->ksize < 3 || m->nitr < 0)) return VIP_E_KSIZE;
+    wait_workers(m);
+    DeviceGuard guard;
+    std::vector<int> rcs(m->n, VIP_OK);
+    std::vector<std::thread> th;
+    th.reserve(m->n);
+    for (int i = 0; i < m->n; i++)
+        th.emplace_back([=, &rcs] { rcs[i] = batch_run_slot(m, i, filter_set, h_src, h_dst, n_frames); });
+    for (auto& t : th) t.join();
+    for (int rc : rcs)
+        if (rc != VIP_OK) return rc;
+    return VIP_OK;
+}
+
+int vip_mg_run_batch_host(vip_mg* m, const uint8_t* h_src, uint8_t* h_dst, int n_frames) {
+    if (!m) return VIP_E_NULL;
+    uint8_t* dst[3] = {nullptr, nullptr, nullptr};
+    dst[m->kind] = h_dst;   // VIP_MG_BF / ABF / BTF = 0 / 1 / 2 = the bit positions of VIP_MG_SET_*
+    return vip_mg_run_batch_set_host(m, 1 << m->kind, h_src, dst, n_frames);
+}
+
+int vip_mg_peer_access(const vip_mg* m) {
+    if (!m) return VIP_E_NULL;
+    int all = 1;
+    for (const Slot& s : m->slots)
+        if (s.peer_up == 0 || s.peer_dn == 0) all = 0;
+    return all;
 }
 
 }  // extern "C"

@@ -347,14 +347,15 @@ class MultiGpuFilter:
     BTF_HALO = {None: 0, "auto": 0, "exchange": capi.VIP_MG_FLAG_BTF_EXCHANGE, "deep": capi.VIP_MG_FLAG_BTF_DEEP_HALO}
 
     def __init__(self, device_ids, kind, width, height, ksize=9, sigma_space=10.0, sigma_color=30.0, nitr=3,
-                 btf_halo=None):
+                 btf_halo=None, require_p2p=False):
         """btf_halo: 'deep' (nitr x 17 halo rows, redundant recompute, no communication), 'exchange' (17 rows refreshed
         peer-to-peer after every iteration) or None / 'auto' (vip_mg_create_ex decides)."""
         self.width, self.height, self.n = width, height, len(device_ids)
         ids = (C.c_int * len(device_ids))(*device_ids)
         self._h = C.c_void_p()
         check(lib().vip_mg_create_ex(C.byref(self._h), ids, len(device_ids), self.KINDS[kind], width, height, ksize,
-                                     sigma_space, sigma_color, nitr, self.BTF_HALO[btf_halo]), "vip_mg_create_ex")
+                                     sigma_space, sigma_color, nitr,
+                                     self.BTF_HALO[btf_halo] | (capi.VIP_MG_FLAG_REQUIRE_P2P if require_p2p else 0)), "vip_mg_create_ex")
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
@@ -395,6 +396,21 @@ class MultiGpuFilter:
         self.run()
         self.gather_host(h_dst)
         return h_dst
+
+    def peer_access(self):
+        """True: halo rows move GPU<->GPU with peer access enabled; False: some neighbour pair stages through the host."""
+        return bool(lib().vip_mg_peer_access(self._h))
+
+    def execute_batch_set(self, h_src, h_dsts, n_frames, filters=("bf", "abf", "btf")):
+        """Every frame through a SET of filters (configs[4]): one upload per frame, h_dsts[name] receives filter `name`."""
+        bits = {"bf": capi.VIP_MG_SET_BF, "abf": capi.VIP_MG_SET_ABF, "btf": capi.VIP_MG_SET_BTF}
+        mask, arr = 0, (C.c_void_p * 3)()
+        for j, name in enumerate(("bf", "abf", "btf")):
+            if name in filters:
+                mask |= bits[name]
+                arr[j] = h_dsts[name].ctypes.data
+        check(lib().vip_mg_run_batch_set_host(self._h, mask, h_src.ctypes.data, arr, n_frames), "vip_mg_run_batch_set_host")
+        return h_dsts
 
     def execute_batch(self, h_src, h_dst, n_frames):
         check(lib().vip_mg_run_batch_host(self._h, h_src.ctypes.data, h_dst.ctypes.data, n_frames),
