@@ -384,16 +384,67 @@ class Job:
             mine = {"src": [vip.ipc_export(b) for b in self.src], "slot": [vip.ipc_export(sl["src"]) for sl in self.slots],
                     "link": self.link.export(), "plan": tuple(plans[rank]), "device": ctx.device_index}
             every = ctx.all_gather_object(mine)
-            for side, r in (("above", rank - 1), ("below", rank + 1)):
-                if 0 <= r < world:
-                    o = every[r]
-                    self.nbr[side] = {"src": [vip.ipc_open(hd) for hd in o["src"]], "slot": [vip.ipc_open(hd) for hd in o["slot"]],
-                                      "plan": o["plan"]}
-            self.link.connect(every[rank - 1]["link"] if rank > 0 else None, every[rank + 1]["link"] if rank < world - 1 else None)
-            self.transport = "cuda-ipc peer pointers over NVLink (%s)" % (
-                "halo rows staged by the filter kernel straight from the neighbours' buffers" if self.halo_mode == "fused"
-                else "cudaMemcpyAsync peer copies of the halo rows")
+            ok = os.environ.get("VIP_BENCH_TRANSPORT", "ipc") != "nccl"
+            if ok:
+                try:
+                    for side, r in (("above", rank - 1), ("below", rank + 1)):
+                        if 0 <= r < world:
+                            o = every[r]
+                            self.nbr[side] = {"src": [vip.ipc_open(hd) for hd in o["src"]],
+                                              "slot": [vip.ipc_open(hd) for hd in o["slot"]], "plan": o["plan"]}
+                    self.link.connect(every[rank - 1]["link"] if rank > 0 else None,
+                                      every[rank + 1]["link"] if rank < world - 1 else None)
+                except vip.VipError as exc:      # no peer path / IPC not permitted here: said in the line, never silent
+                    ok = False
+                    self.ipc_error = str(exc)
+            # every rank takes the same transport
+            if not all(ctx.all_gather_object(ok)):
+                self._close_ipc()
+                self.link = None
+                self.halo_mode = "nccl"
+                for side, r in (("above", rank - 1), ("below", rank + 1)):
+                    if 0 <= r < world:
+                        self.nbr[side] = {"rank": r, "plan": every[r]["plan"]}
+                self.transport = ("NCCL send/recv of the halo rows (torch.distributed), because CUDA IPC between the ranks is not available here: "
+                                  + getattr(self, "ipc_error", os.environ.get("VIP_BENCH_TRANSPORT", "")))
+            else:
+                self.transport = "cuda-ipc peer pointers over NVLink (%s)" % (
+                    "halo rows staged by the filter kernel straight from the neighbours' buffers" if self.halo_mode == "fused"
+                    else "cudaMemcpyAsync peer copies of the halo rows")
         ctx.barrier()
+
+    def _close_ipc(self):
+        for side in self.nbr.values():
+            for p in side.get("src", []) + side.get("slot", []):
+                try:
+                    self.vip.ipc_close(p)
+                except self.vip.VipError:
+                    pass
+        self.nbr = {}
+
+    def _view(self, img, row0, rows):
+        """torch uint8 view of rows [row0, row0 + rows) of a DeviceImage (zero copy), for the NCCL fallback"""
+        class V:
+            pass
+        v = V()
+        v.__cuda_array_interface__ = {"shape": (rows * self.rb,), "typestr": "|u1", "data": (img.row_ptr(row0), False), "version": 2}
+        return self.ctx.torch.as_tensor(v, device="cuda")
+
+    def _exchange_halo_nccl(self, img, stream):
+        """fallback transport: the rows the neighbours need are sent, the halo rows received, through NCCL"""
+        torch, dist = self.ctx.torch, self.ctx.dist
+        ops = []
+        with torch.cuda.stream(stream) if stream is not None else torch.cuda.stream(torch.cuda.current_stream()):
+            if "above" in self.nbr:
+                r = self.nbr["above"]["rank"]
+                ops.append(dist.P2POp(dist.isend, self._view(img, self.y0 - self.s0, self.halo), r))
+                ops.append(dist.P2POp(dist.irecv, self._view(img, 0, self.y0 - self.s0), r))
+            if "below" in self.nbr:
+                r = self.nbr["below"]["rank"]
+                ops.append(dist.P2POp(dist.isend, self._view(img, self.y1 - self.s0 - self.halo, self.halo), r))
+                ops.append(dist.P2POp(dist.irecv, self._view(img, self.y1 - self.s0, self.s1 - self.y1), r))
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
 
     # strip descriptors ---------------------------------------------------------------------------------------------
     def _peer_halo(self, which, j):
@@ -441,7 +492,10 @@ class Job:
             else:
                 self.F.execute_strip_peer(own_ptr, halo, dst_imgs[0], st, stream=stream)
             return
-        self._pull_halo(which, j, src_img, stream)
+        if self.halo_mode == "nccl":
+            self._exchange_halo_nccl(src_img, stream)
+        else:
+            self._pull_halo(which, j, src_img, stream)
         if filt in ("bf", "abf"):
             st = vip.Strip(self.s0, self.s1 - self.s0, self.y0, self.y0, self.own)
             if filt == "bf":
@@ -531,10 +585,7 @@ class Job:
     def close(self):
         """unmap the neighbours' buffers before anybody frees them"""
         self.ctx.barrier()
-        for side in self.nbr.values():
-            for p in side["src"] + side["slot"]:
-                self.vip.ipc_close(p)
-        self.nbr = {}
+        self._close_ipc()
         self.link = None
         self.ctx.barrier()
 
@@ -730,7 +781,9 @@ def measure_job(ctx, name, steps, warmup, halo_mode, sampler=None, with_cpu=True
 
     out = {
         "metric": f"{filt}_throughput", "value": value, "unit": "Mpixel/s", "ms_per_step": ms_step, "steps": steps, "warmup": warmup,
-        "scaling": "strong" if job.strong else "weak",
+        # one frame's work is fixed and cut into N strips (strong) wherever the filter and the frame allow it -- at N = 1 the
+        # cut is the whole frame; only the frame stream / tiny frames give every GPU its own frames (weak)
+        "scaling": "strong" if (job.strong or (ctx.world == 1 and filt != "all")) else "weak",
         "config": {"workload": name, "description": job.desc, "width": w, "height": h, "ksize": ksize, "nitr": nitr,
                    "content": ctx.args.content,
                    "parallelism": (f"{ctx.world} row strips of one frame, one process per {'rank (ranks SHARE a GPU: functional test, not a measurement)' if ctx.shared_gpu else 'GPU'}; halo {job.halo} rows per side; {job.transport}"

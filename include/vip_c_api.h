@@ -103,6 +103,8 @@ typedef struct vip_stencil_plan {
     int lut_clamped;  /* 1: the index is clamped to lut_entries - 1                                                */
     int warp_groups;  /* 256-thread warp groups per CTA (one CTA per SM)                                           */
     int smem_bytes;   /* dynamic shared memory per CTA                                                             */
+    int lut_rows;     /* 1, or the rows of a PREMULTIPLIED table: one row RN(ks * lut[i]) per distinct spatial weight, */
+                      /* which takes the multiply out of every tap (short tables only: sigma_color of a few levels)   */
 } vip_stencil_plan;
 VIP_API int vip_stencil_plan_query(int mode, int ksize, float sigma_space, float sigma_color, vip_stencil_plan* out);
 
@@ -231,6 +233,9 @@ typedef struct vip_btf vip_btf;
 VIP_API int vip_btf_create(vip_btf** out, int width, int height, int ksize, int nitr);
 VIP_API int vip_btf_destroy(vip_btf* f);
 VIP_API int vip_btf_run(vip_btf* f, const uint8_t* d_src, uint8_t* d_dst, void* stream);
+/* Replay the 3 x nitr launches of vip_btf_run as ONE captured CUDA graph per (d_src, d_dst) pair (up to 32 pairs are
+ * kept).  Off by default; only on non-default streams.  Results are identical either way. */
+VIP_API int vip_btf_set_graph(vip_btf* f, int on);
 VIP_API int vip_btf_blur_rtv(const vip_btf* f, const uint8_t* d_image, const float* d_magnitude, float* d_blurred,
                              float* d_rtv, void* stream);
 VIP_API int vip_btf_guide(const vip_btf* f, const float* d_blurred, const float* d_rtv, uint8_t* d_guide,

@@ -4,6 +4,10 @@
   python tools/ncu_summary.py launches <launches.csv> [...]      per-kernel launch counts, mean time, share of the step
   python tools/ncu_summary.py full <prof.ncu-rep> [...]          key metrics of each profiled launch (ncu --set full)
   python tools/ncu_summary.py traffic <name>=<prof.ncu-rep> ...  JSON {name: dram bytes per launch} for bench.py
+  python tools/ncu_summary.py constants <key>=<prof.ncu-rep>:<pixels>:<taps per pixel> ...
+                                                                 profiles/ncu_constants.json: what bench.py reports as
+                                                                 issue.util_ncu / roofline.traffic (hardware counters of the
+                                                                 FINAL tree's kernels, never literals in bench.py)
 """
 import collections
 import csv
@@ -97,5 +101,54 @@ def cmd_traffic(specs):
     print(json.dumps(out, indent=1))
 
 
+CONST_METRICS = {
+    "gpu__time_duration.sum": "duration",
+    "smsp__inst_executed.sum": "warp_inst_executed",
+    "smsp__inst_issued.sum": "warp_inst_issued",
+    "smsp__issue_active.avg.pct_of_peak_sustained_active": "issue_active_pct",
+    "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active": "pipe_fma_cycles_active_pct",
+    "sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_active": "pipe_fmaheavy_cycles_active_pct",
+    "sm__pipe_fmalite_cycles_active.avg.pct_of_peak_sustained_active": "pipe_fmalite_cycles_active_pct",
+    "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active": "inst_pipe_fma_pct",
+    "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active": "inst_pipe_alu_pct",
+    "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active": "inst_pipe_xu_pct",
+    "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active": "inst_pipe_lsu_pct",
+    "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum": "shared_wavefronts",
+    "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum": "shared_bank_conflicts",
+    "launch__registers_per_thread": "registers_per_thread",
+}
+
+
+def cmd_constants(specs):
+    out = {}
+    for spec in specs:
+        key, rest = spec.split("=", 1)
+        path, pixels, taps = rest.rsplit(":", 2)
+        hdr, units, rows = raw_rows(path)
+        v = rows[0]
+        d = {"source": path.split("/")[-1], "kernel": v[hdr.index("Kernel Name")][:80], "launches_in_report": len(rows)}
+        for m, label in CONST_METRICS.items():
+            if m in hdr:
+                i = hdr.index(m)
+                d[label] = float(v[i].replace(",", ""))
+                if label == "duration":
+                    d["duration_unit"] = units[i]
+        d["dram_bytes_per_launch"] = sum(to_bytes(v[hdr.index(m)], units[hdr.index(m)])
+                                         for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+        n_taps = float(pixels) * float(taps)
+        d["pixels"], d["taps_per_pixel"] = int(pixels), int(taps)
+        d["thread_instr_per_tap"] = d["warp_inst_executed"] * 32 / n_taps      # whole kernel: staging, prologue, epilogue included
+        stalls = []
+        for i, n in enumerate(hdr):
+            if n.startswith(STALL_PREFIX) and n.endswith("_per_issue_active.ratio") and "not_issued" not in n:
+                try:
+                    stalls.append((float(v[i]), n[len(STALL_PREFIX):-len("_per_issue_active.ratio")]))
+                except ValueError:
+                    pass
+        d["top_stalls_per_issue_active"] = {n: round(x, 2) for x, n in sorted(stalls, reverse=True)[:5]}
+        out[key] = d
+    print(json.dumps(out, indent=1))
+
+
 if __name__ == "__main__":
-    {"launches": cmd_launches, "full": cmd_full, "traffic": cmd_traffic}[sys.argv[1]](sys.argv[2:])
+    {"launches": cmd_launches, "full": cmd_full, "traffic": cmd_traffic, "constants": cmd_constants}[sys.argv[1]](sys.argv[2:])

@@ -43,7 +43,7 @@ class Halo(C.Structure):
 class StencilPlan(C.Structure):
     """struct vip_stencil_plan: how a bilateral-family filter will run (host logic, answers without a GPU)."""
     _fields_ = [("tiled", C.c_int), ("lut_entries", C.c_int), ("lut_copies", C.c_int), ("lut_clamped", C.c_int),
-                ("warp_groups", C.c_int), ("smem_bytes", C.c_int)]
+                ("warp_groups", C.c_int), ("smem_bytes", C.c_int), ("lut_rows", C.c_int)]
 
 
 class MgPlan(C.Structure):
@@ -106,6 +106,7 @@ SIGNATURES = {
     "vip_btf_create": (_i, [_pp, _i, _i, _i, _i]),
     "vip_btf_destroy": (_i, [_vp]),
     "vip_btf_run": (_i, [_vp, _vp, _vp, _vp]),
+    "vip_btf_set_graph": (_i, [_vp, _i]),
     "vip_btf_blur_rtv": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "vip_btf_guide": (_i, [_vp, _vp, _vp, _vp, _vp]),
     "vip_btf_halo_rows_per_iteration": (_i, [_vp]),

@@ -2,6 +2,7 @@
 // orchestration.  Host logic only -- the kernels live in stencil.cu / gradient.cu / btf.cu / integral.cu.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <atomic>
 #include <cmath>
 #include <cstdlib>
@@ -51,6 +52,10 @@ struct StencilTables {
     int device = 0, sm_count = 0;
     std::vector<float> h_ks, h_lut;
     DeviceBuf d_lut, d_hw, d_ks, d_wrows;
+    // premultiplied table (stencil.cu kLutPremul): one row of pm_n entries RN(ks * lut[i]) per distinct spatial weight,
+    // and the weight rows with every tap's row offset (bytes in the 32x replicated shared-memory table) as int bits
+    int n_ks = 0, pm_n = 0;
+    DeviceBuf d_lut_pm, d_wrows_pm;
 };
 
 int validate(int width, int height, int ksize, float ss, float sc) {
@@ -136,6 +141,42 @@ int init_tables(StencilTables& T, int width, int height, int ksize, float ss, fl
     if ((e = T.d_wrows.alloc(w_rows.size() * sizeof(float))) != cudaSuccess) return cu(e);
     if ((e = cudaMemcpy(T.d_wrows.p, w_rows.data(), w_rows.size() * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess)
         return cu(e);
+    // distinct non-zero spatial weights; when the colour table is short enough for one premultiplied row per weight
+    // (vip::stencil_pick_lut decides, per mode), build those rows: RN(ks * lut[i]) is the product the tap's FMUL rounds to
+    std::vector<float> dk;
+    for (float v : T.h_ks)
+        if (v != 0.f && std::find(dk.begin(), dk.end(), v) == dk.end()) dk.push_back(v);
+    T.n_ks = static_cast<int>(dk.size());
+    bool want_pm = false;
+    if (table_len == 768) {
+        for (int mode = 0; mode < 2; mode++) {
+            int n = 0, kind = 0;
+            vip::stencil_pick_lut(static_cast<vip::StencilMode>(mode), r, table_len, T.last_nz, T.n_ks, &n, &kind);
+            if (kind == vip::kStencilLutPremul) {
+                want_pm = true;
+                T.pm_n = n;
+            }
+        }
+    }
+    if (want_pm) {
+        std::vector<float> pm(static_cast<size_t>(T.n_ks) * T.pm_n);
+        for (int d = 0; d < T.n_ks; d++)
+            for (int i = 0; i < T.pm_n; i++) {
+                volatile float prod = dk[d] * T.h_lut[i];   // one IEEE single multiply, no contraction / excess precision
+                pm[static_cast<size_t>(d) * T.pm_n + i] = prod;
+            }
+        std::vector<std::uint32_t> offs(w_rows.size(), 0u);
+        for (size_t i = 0; i < w_rows.size(); i++) {
+            if (w_rows[i] == 0.f) continue;
+            const int d = static_cast<int>(std::find(dk.begin(), dk.end(), w_rows[i]) - dk.begin());
+            offs[i] = static_cast<std::uint32_t>(d) * T.pm_n * 128u;
+        }
+        if ((e = T.d_lut_pm.alloc(pm.size() * sizeof(float))) != cudaSuccess) return cu(e);
+        if ((e = cudaMemcpy(T.d_lut_pm.p, pm.data(), pm.size() * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess) return cu(e);
+        if ((e = T.d_wrows_pm.alloc(offs.size() * sizeof(std::uint32_t))) != cudaSuccess) return cu(e);
+        if ((e = cudaMemcpy(T.d_wrows_pm.p, offs.data(), offs.size() * sizeof(std::uint32_t), cudaMemcpyHostToDevice)) != cudaSuccess)
+            return cu(e);
+    }
     return VIP_OK;
 }
 
@@ -187,10 +228,16 @@ int run_stencil(const StencilTables& T, vip::StencilMode mode, const uint8_t* d_
     a.out_rows = s.out_rows;
     a.radius = T.radius;
     a.lut = static_cast<const float*>(T.d_lut.p);
-    vip::stencil_pick_lut(mode, T.radius, T.table_len, T.last_nz, &a.lut_n, &a.lut_kind);
+    vip::stencil_pick_lut(mode, T.radius, T.table_len, T.last_nz, T.n_ks, &a.lut_n, &a.lut_kind);
+    a.lut_rows = 1;
     a.hw = static_cast<const int*>(T.d_hw.p);
     a.ks_full = static_cast<const float*>(T.d_ks.p);
     a.w_rows = static_cast<const float*>(T.d_wrows.p);
+    if (a.lut_kind == vip::kStencilLutPremul) {
+        a.lut = static_cast<const float*>(T.d_lut_pm.p);
+        a.w_rows = static_cast<const float*>(T.d_wrows_pm.p);
+        a.lut_rows = T.n_ks;
+    }
     return cu(vip::launch_stencil(mode, a, T.sm_count, static_cast<cudaStream_t>(stream)));
 }
 
@@ -208,10 +255,20 @@ struct vip_image {
     int width, height, channels, elem_size;
     DeviceBuf buf;
 };
+struct BtfGraph {
+    const uint8_t* src;
+    uint8_t* dst;
+    cudaGraphExec_t exec;
+};
 struct vip_btf {
     int width, height, ksize, nitr, scratch_rows;
     vip_bf* jbf;
     DeviceBuf ping, pong, blurred, rtv, guide;
+    // CUDA-graph replay of the 3 x nitr launches of a run: one captured graph per (src, dst) pair,
+    // programmatic-dependent-launch edges included.  Off by default (see DESIGN.md 3.2 for the measured A/B);
+    // vip_btf_set_graph() or VIP_BTF_GRAPH=1 switches it on.
+    bool use_graph = false;
+    std::vector<BtfGraph> graphs;
 };
 
 extern "C" {
@@ -248,13 +305,18 @@ int vip_stencil_plan_query(int mode, int ksize, float sigma_space, float sigma_c
     while (last_nz > 0 && lut[last_nz] == 0.f) last_nz--;
     const int radius = ksize / 2;
     int lut_n = table_len, kind = 0;
-    vip::stencil_pick_lut(static_cast<vip::StencilMode>(mode), radius, table_len, last_nz, &lut_n, &kind);
+    std::vector<float> dk;
+    for (float v : ks)
+        if (v != 0.f && std::find(dk.begin(), dk.end(), v) == dk.end()) dk.push_back(v);
+    vip::stencil_pick_lut(static_cast<vip::StencilMode>(mode), radius, table_len, last_nz, static_cast<int>(dk.size()), &lut_n,
+                          &kind);
     std::memset(out, 0, sizeof(*out));
     out->tiled = radius <= vip::stencil_max_tiled_radius() ? 1 : 0;
     out->lut_entries = lut_n;
+    out->lut_rows = kind == vip::kStencilLutPremul ? static_cast<int>(dk.size()) : 1;
     if (out->tiled)
-        vip::stencil_describe(static_cast<vip::StencilMode>(mode), radius, lut_n, kind, &out->lut_copies, &out->lut_clamped,
-                              &out->warp_groups, &out->smem_bytes);
+        vip::stencil_describe(static_cast<vip::StencilMode>(mode), radius, lut_n, out->lut_rows, kind, &out->lut_copies,
+                              &out->lut_clamped, &out->warp_groups, &out->smem_bytes);
     return VIP_OK;
 }
 
@@ -505,6 +567,10 @@ static int btf_create_rows(vip_btf** out, int width, int height, int ksize, int 
     f->nitr = nitr;
     f->scratch_rows = scratch_rows;
     f->jbf = nullptr;
+    {
+        const char* v = std::getenv("VIP_BTF_GRAPH");
+        f->use_graph = v && v[0] == '1';
+    }
     // src/bilateral_texture_filter_impl.cu:188 and .cuh:31: (ksize 2k-1, sigma_space k-1, sigma_color sqrt(3))
     int rc = VIP_OK;
     if (ksize > 1) {
@@ -538,6 +604,8 @@ int vip_btf_create_rows_internal(vip_btf** out, int width, int height, int ksize
     return btf_create_rows(out, width, height, ksize, nitr, scratch_rows);
 }
 int vip_btf_destroy(vip_btf* f) {
+    if (f)
+        for (BtfGraph& g : f->graphs) cudaGraphExecDestroy(g.exec);
     if (f && f->jbf) vip_bf_destroy(f->jbf);
     delete f;
     return VIP_OK;
@@ -589,9 +657,48 @@ int vip_btf_iterate_strip(vip_btf* f, const uint8_t* d_src_n, uint8_t* d_dst_n, 
     return vip_jbf_run_strip(f->jbf, d_src_n, gd, d_dst_n, s, stream);
 }
 
+static int btf_enqueue(vip_btf* f, const uint8_t* d_src, uint8_t* d_dst, void* stream);
+
+int vip_btf_set_graph(vip_btf* f, int on) {
+    if (!f) return VIP_E_NULL;
+    f->use_graph = on != 0;
+    return VIP_OK;
+}
+
 int vip_btf_run(vip_btf* f, const uint8_t* d_src, uint8_t* d_dst, void* stream) {
     if (!f || !d_src || !d_dst) return VIP_E_NULL;
     if (f->scratch_rows < f->height) return VIP_E_STRIP;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // graph replay: not on the legacy default stream (it cannot be captured) and not for the trivial nitr = 0 copy
+    if (!f->use_graph || f->nitr == 0 || st == nullptr || st == cudaStreamLegacy) return btf_enqueue(f, d_src, d_dst, stream);
+    for (const BtfGraph& g : f->graphs)
+        if (g.src == d_src && g.dst == d_dst) {
+            vip::count_launch(3 * f->nitr);
+            return cu(cudaGraphLaunch(g.exec, st));
+        }
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed);
+    if (e != cudaSuccess) return cu(e);
+    const int rc = btf_enqueue(f, d_src, d_dst, stream);
+    e = cudaStreamEndCapture(st, &graph);
+    if (rc != VIP_OK || e != cudaSuccess) {
+        if (graph) cudaGraphDestroy(graph);
+        cudaGetLastError();
+        return rc != VIP_OK ? rc : cu(e);
+    }
+    cudaGraphExec_t exec = nullptr;
+    e = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) return cu(e);
+    if (f->graphs.size() >= 32) {   // bounded cache: forget the oldest pair
+        cudaGraphExecDestroy(f->graphs.front().exec);
+        f->graphs.erase(f->graphs.begin());
+    }
+    f->graphs.push_back(BtfGraph{d_src, d_dst, exec});
+    return cu(cudaGraphLaunch(exec, st));
+}
+
+static int btf_enqueue(vip_btf* f, const uint8_t* d_src, uint8_t* d_dst, void* stream) {
     const size_t bytes = static_cast<size_t>(f->width) * f->height * 3;
     if (f->nitr == 0)  // the reference copies src -> dst_n -> dst (:203, :213)
         return cu(cudaMemcpyAsync(d_dst, d_src, bytes, cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));

@@ -102,6 +102,10 @@ __global__ void __launch_bounds__(256) gradient_u8c3_fast_kernel(const std::uint
                                                                  const int out_y0, const int out_rows) {
     const int x = 4 * (blockIdx.x * 32 + threadIdx.x);
     const int y0 = out_y0 + (blockIdx.y * 8 + threadIdx.y) * kFastRows;
+    // launched through launch_pdl: the kernel is 10 - 50 us long, so the launch gap between it and its predecessor is a
+    // visible share of it; the previous grid has completed and flushed from pdl_wait() on
+    pdl_wait();
+    pdl_release();
     if (x >= W || y0 >= out_y0 + out_rows) return;
     const int wpr = (W * 3) >> 2;  // words per row
     auto row_ptr = [&](int yy) {
@@ -185,8 +189,10 @@ cudaError_t launch_gradient_u8(const std::uint8_t* src, float* dst, int width, i
         (reinterpret_cast<std::uintptr_t>(dst) & 15u) == 0) {
         const dim3 block(32, 8);
         const dim3 grid((width / 4 + 31) / 32, (out_rows + 8 * kFastRows - 1) / (8 * kFastRows));
-        gradient_u8c3_fast_kernel<<<grid, block, 0, stream>>>(src, dst, width, height, src_y0, src_rows, dst_y0, out_y0,
-                                                              out_rows);
+        const cudaError_t e = launch_pdl(gradient_u8c3_fast_kernel, grid, block, 0, stream, src, dst, width, height, src_y0,
+                                         src_rows, dst_y0, out_y0, out_rows);
+        count_launch();
+        return e;
     } else if (channels == 3 || channels == 1) {
         const dim3 grid((width + kGradCols - 1) / kGradCols, (out_rows + kGradRowsPerCta - 1) / kGradRowsPerCta);
         if (channels == 3)

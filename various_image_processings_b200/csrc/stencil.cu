@@ -127,7 +127,11 @@ __device__ __forceinline__ void load_packed4(const std::uint8_t* __restrict__ p,
 //   kLutNarrow   every entry 8 times (32 B), clamped: for tables too long for 32 copies next to the tile buffers (ABF
 //                with a wide sigma_color: 1536 entries x 128 B = 192 KB); lanes l and l+8k share a copy, so two
 //                different indices can meet in a bank (<= 4-way, ~1.5 on average) -- only the LDS of the tap replays
-enum LutKind { kLutFull = 0, kLutClamp = 1, kLutNarrow = 2 };
+//   kLutPremul   BF / JBF with a SHORT table (sigma_color of a few levels: the joint bilateral step of the texture filter has
+//                sqrt 3, 27 entries): one 32x replicated, clamped row PER DISTINCT SPATIAL WEIGHT, holding RN(ks * lut[i])
+//                -- the very float the tap's FMUL would produce -- so the FMUL disappears from the tap (7 -> 6 issue slots);
+//                the weight rows then hold the byte offset of each tap's table row instead of its weight
+enum LutKind { kLutFull = 0, kLutClamp = 1, kLutNarrow = 2, kLutPremul = 3 };
 __host__ __device__ constexpr bool lut_clamped(const int lk) { return lk != kLutFull; }
 __host__ __device__ constexpr int lut_shift(const int lk) { return lk == kLutNarrow ? 5 : 7; }  // log2(bytes per entry)
 // bits(2^23 + i) << shift, modulo 2^32, for i = 0: what abf_weight's shifted float bits carry on top of (i << shift)
@@ -146,30 +150,47 @@ __device__ __forceinline__ float byte_to_float(const std::uint32_t v) {
     return static_cast<float>((v >> (8 * BYTE)) & 0xffu);
 }
 
-// A run of L consecutive taps (kx0 .. kx0+L-1) of one window row for the P outputs of this thread.
-// t points at the tile element of (first output, kx0); wp at the L weights of the run (16-byte aligned,
-// readable up to the next multiple of 4).  Per accumulator the taps are visited in increasing kx.
-template <int MODE, int P, int L, int LK>
+// A PIECE of one window row for the P outputs of this thread: the NN consecutive tile elements t[0 .. NN) ("neighbours")
+// and, of the taps they form with the outputs -- neighbour n is tap j = n - i of output i --, those with JLO <= j < JHI.
+// t points at the tile element of (first output, tap 0 of the piece), wp at the weight of tap 0 (16-byte aligned; taps
+// down to JLO lie before it).  Per accumulator the taps are visited in increasing j, i.e. increasing kx.
+//   a whole short row of L taps (or a run of 8 of the old decomposition): NN = P + L - 1, JLO = 0, JHI = L
+//   sliding decomposition of a long row (do_row): first 8 neighbours <8, 0, 8>, then steady blocks of 8 neighbours in
+//   which every output has a tap <8, -(P-1), 8>, then the last r taps and the P - 1 neighbours only the later outputs
+//   still see <r + P - 1, -(P-1), r>.  Every tile element of the row is then loaded and converted ONCE (the runs of 8
+//   re-read the 7 elements two runs share: 0.25 instead of 0.16 elements per tap at r = 15).
+__host__ __device__ constexpr int floor4(const int v) { return v >= 0 ? (v & ~3) : -((-v + 3) & ~3); }
+
+template <int MODE, int P, int NN, int JLO, int JHI, int LK>
 __device__ __forceinline__ void run_taps(const typename Elem<MODE>::type* __restrict__ t, const float* __restrict__ wp,
                                          const std::uint32_t lut_addr, const std::uint32_t clamp_i, const float clamp_f,
                                          Acc<MODE, P>& A) {
-    float w[(L + 3) & ~3];
+    constexpr int WOFF = floor4(JLO), NW = (JHI - WOFF + 3) & ~3;   // weights w[j - WOFF] of taps WOFF .. WOFF + NW
+    float w[NW];
 #pragma unroll
-    for (int j = 0; j < (L + 3) / 4; ++j) {
-        const float4 v = reinterpret_cast<const float4*>(wp)[j];
+    for (int j = 0; j < NW / 4; ++j) {
+        const float4 v = reinterpret_cast<const float4*>(wp + WOFF)[j];
         w[4 * j + 0] = v.x;
         w[4 * j + 1] = v.y;
         w[4 * j + 2] = v.z;
         w[4 * j + 3] = v.w;
     }
     const unsigned long long one2 = pack2(1.f, 1.f);
+    if constexpr (LK == kLutPremul) {
+        // w[] carries the byte offset of each tap's table row; fold this lane's copy address in once per piece
+#pragma unroll
+        for (int j = JLO; j < JHI; ++j) w[j - WOFF] = __uint_as_float(__float_as_uint(w[j - WOFF]) + lut_addr);
+    }
     auto weight = [&](const std::uint32_t q, const std::uint32_t c, const float ks) {
         std::uint32_t sad = __vsadu4(q, c);
         if constexpr (lut_clamped(LK)) sad = min(sad, clamp_i);
-        return __fmul_rn(ks, lds_f32(lut_addr + (sad << lut_shift(LK))));
+        if constexpr (LK == kLutPremul)
+            return lds_f32(__float_as_uint(ks) + (sad << lut_shift(LK)));   // the row holds RN(ks * lut[sad]) already
+        else
+            return __fmul_rn(ks, lds_f32(lut_addr + (sad << lut_shift(LK))));
     };
 #pragma unroll
-    for (int n = 0; n < P + L - 1; ++n) {
+    for (int n = 0; n < NN; ++n) {
         std::uint32_t q, v;
         if constexpr (MODE == kJBF) {
             const uint2 e = t[n];
@@ -186,14 +207,14 @@ __device__ __forceinline__ void run_taps(const typename Elem<MODE>::type* __rest
 #pragma unroll
         for (int p = 0; p < P / 2; ++p) {
             const int j = n - 2 * p;  // tap of output 2p; output 2p+1 sees tap j-1
-            const bool lo = j >= 0 && j < L, hi = j - 1 >= 0 && j - 1 < L;
+            const bool lo = j >= JLO && j < JHI, hi = j - 1 >= JLO && j - 1 < JHI;
             float wl = 0.f, wh = 0.f;
             if (lo) {
-                wl = weight(q, A.c[2 * p], w[j]);
+                wl = weight(q, A.c[2 * p], w[lo ? j - WOFF : 0]);
                 fma2(A.s01[2 * p], f01, pack2(wl, wl));
             }
             if (hi) {
-                wh = weight(q, A.c[2 * p + 1], w[j - 1]);
+                wh = weight(q, A.c[2 * p + 1], w[hi ? j - 1 - WOFF : 0]);
                 fma2(A.s01[2 * p + 1], f01, pack2(wh, wh));
             }
             if (lo && hi) {
@@ -233,13 +254,14 @@ __device__ __forceinline__ float abf_weight(const float d0, const float d1, cons
 // ABF run: outputs are handled in pairs (2p, 2p+1).  Neighbour n is tap j = n - 2p of the first and tap j - 1 of
 // the second output; when both are inside the run the differences and the four accumulations are packed fp32x2
 // operations (same IEEE roundings per half as the scalar ones), otherwise the one valid output goes scalar.
-template <int P, int L, int LK>
+template <int P, int NN, int JLO, int JHI, int LK>
 __device__ __forceinline__ void run_taps_abf(const std::uint32_t* __restrict__ t, const float* __restrict__ wp,
                                              const std::uint32_t lut_addr, const float clamp_f, Acc<kABF, P>& A) {
-    float w[(L + 3) & ~3];
+    constexpr int WOFF = floor4(JLO), NW = (JHI - WOFF + 3) & ~3;
+    float w[NW];
 #pragma unroll
-    for (int j = 0; j < (L + 3) / 4; ++j) {
-        const float4 v = reinterpret_cast<const float4*>(wp)[j];
+    for (int j = 0; j < NW / 4; ++j) {
+        const float4 v = reinterpret_cast<const float4*>(wp + WOFF)[j];
         w[4 * j + 0] = v.x;
         w[4 * j + 1] = v.y;
         w[4 * j + 2] = v.z;
@@ -247,7 +269,7 @@ __device__ __forceinline__ void run_taps_abf(const std::uint32_t* __restrict__ t
     }
     const unsigned long long one2 = pack2(1.f, 1.f);
 #pragma unroll
-    for (int n = 0; n < P + L - 1; ++n) {
+    for (int n = 0; n < NN; ++n) {
         const std::uint32_t v = t[n];
         const float f0 = byte_to_float<0>(v);
         const float f1 = byte_to_float<1>(v);
@@ -255,7 +277,7 @@ __device__ __forceinline__ void run_taps_abf(const std::uint32_t* __restrict__ t
 #pragma unroll
         for (int p = 0; p < P / 2; ++p) {
             const int j = n - 2 * p;  // tap of output 2p; output 2p+1 sees tap j-1
-            const bool lo = j >= 0 && j < L, hi = j - 1 >= 0 && j - 1 < L;
+            const bool lo = j >= JLO && j < JHI, hi = j - 1 >= JLO && j - 1 < JHI;
             if (lo && hi) {
                 const unsigned long long d0 = add2(add2(pack2(f0, f0), A.nfp[0][p]), A.noff[0][p]);
                 const unsigned long long d1 = add2(add2(pack2(f1, f1), A.nfp[1][p]), A.noff[1][p]);
@@ -264,8 +286,8 @@ __device__ __forceinline__ void run_taps_abf(const std::uint32_t* __restrict__ t
                 unpack2(d0, d0l, d0h);
                 unpack2(d1, d1l, d1h);
                 unpack2(d2, d2l, d2h);
-                const float wl = abf_weight<LK>(d0l, d1l, d2l, w[j], lut_addr, clamp_f);
-                const float wh = abf_weight<LK>(d0h, d1h, d2h, w[j - 1], lut_addr, clamp_f);
+                const float wl = abf_weight<LK>(d0l, d1l, d2l, w[j - WOFF], lut_addr, clamp_f);
+                const float wh = abf_weight<LK>(d0h, d1h, d2h, w[j - 1 - WOFF], lut_addr, clamp_f);
                 const unsigned long long ww = pack2(wl, wh);
                 fma2(A.s[0][p], ww, pack2(f0, f0));
                 fma2(A.s[1][p], ww, pack2(f1, f1));
@@ -292,7 +314,7 @@ __device__ __forceinline__ void run_taps_abf(const std::uint32_t* __restrict__ t
                 const float d0 = __fadd_rn(__fadd_rn(f0, nf[0]), no[0]);
                 const float d1 = __fadd_rn(__fadd_rn(f1, nf[1]), no[1]);
                 const float d2 = __fadd_rn(__fadd_rn(f2, nf[2]), no[2]);
-                const float wt = abf_weight<LK>(d0, d1, d2, w[jj], lut_addr, clamp_f);
+                const float wt = abf_weight<LK>(d0, d1, d2, w[jj - WOFF], lut_addr, clamp_f);
                 a[0] = __fmaf_rn(f0, wt, a[0]);
                 a[1] = __fmaf_rn(f1, wt, a[1]);
                 a[2] = __fmaf_rn(f2, wt, a[2]);
@@ -304,21 +326,62 @@ __device__ __forceinline__ void run_taps_abf(const std::uint32_t* __restrict__ t
     }
 }
 
-// One window row of len = 2*hw+1 taps: runs of 8, then the odd remainder.
+// One window row of len = 2*hw+1 taps (odd).  Rows of up to 7 taps are one piece.  Longer rows are either cut into runs
+// of 8 taps plus the odd remainder, or SLIDE along the tile row (see run_taps) so that every tile element is loaded and
+// converted once.  Measured on B200 (profiles/r02c_sliding_ab.txt, all bit-exact): sliding executes 3.6 % fewer
+// instructions at BF 8K r=15 (XU pipe 58 -> 38 %) for the SAME 6.85 ms -- the tap loop is bound by the 2-cycle packed
+// fp32x2 instructions on the FMA pipe (ncu: FFMA2 / FADD2 carry 40 % of the stall samples, reason math-pipe throttle),
+// not by the instruction count -- and its 1.7x larger code shows up as instruction-fetch stalls (0.49 per issue); it
+// wins 1.4 % for ABF (4 outputs per thread: the re-read share is largest), loses 3 % at 1080p BF k=9.  Hence: sliding
+// for ABF, runs of 8 for BF / JBF.  -DVIP_SLIDING=0 / =1 forces one decomposition everywhere (A/B builds).
+template <int MODE>
+__host__ __device__ constexpr bool sliding_rows() {
+#if defined(VIP_SLIDING)
+    return VIP_SLIDING != 0;
+#else
+    return MODE == kABF;
+#endif
+}
 template <int MODE, int P, int LK>
 __device__ __forceinline__ void do_row(int len, const typename Elem<MODE>::type* __restrict__ t,
                                        const float* __restrict__ wp, const std::uint32_t lut_addr,
                                        const std::uint32_t clamp_i, const float clamp_f, Acc<MODE, P>& A) {
-    auto run = [&](auto lc) {
-        constexpr int L = decltype(lc)::value;
+    constexpr bool kSlide = sliding_rows<MODE>();
+    auto piece = [&](auto nn, auto jlo, auto jhi) {
+        constexpr int NN = decltype(nn)::value, JLO = decltype(jlo)::value, JHI = decltype(jhi)::value;
         if constexpr (MODE == kABF) {
-            run_taps_abf<P, L, LK>(t, wp, lut_addr, clamp_f, A);
+            run_taps_abf<P, NN, JLO, JHI, LK>(t, wp, lut_addr, clamp_f, A);
         } else {
-            run_taps<MODE, P, L, LK>(t, wp, lut_addr, clamp_i, clamp_f, A);
+            run_taps<MODE, P, NN, JLO, JHI, LK>(t, wp, lut_addr, clamp_i, clamp_f, A);
         }
     };
+    auto run = [&](auto lc) {   // a whole row / run of L taps
+        constexpr int L = decltype(lc)::value;
+        piece(std::integral_constant<int, P + L - 1>{}, std::integral_constant<int, 0>{}, std::integral_constant<int, L>{});
+    };
+    auto tail = [&](auto rc) {  // the last r taps of a sliding row + the P - 1 elements only the later outputs still see
+        constexpr int R = decltype(rc)::value;
+        piece(std::integral_constant<int, R + P - 1>{}, std::integral_constant<int, -(P - 1)>{}, std::integral_constant<int, R>{});
+    };
+    if (kSlide && len >= 9) {
+        piece(std::integral_constant<int, 8>{}, std::integral_constant<int, 0>{}, std::integral_constant<int, 8>{});
+        len -= 8, t += 8, wp += 8;
 #pragma unroll 1
-    for (; len >= 8; len -= 8, t += 8, wp += 8) run(std::integral_constant<int, 8>{});
+        for (; len >= 8; len -= 8, t += 8, wp += 8)
+            piece(std::integral_constant<int, 8>{}, std::integral_constant<int, -(P - 1)>{}, std::integral_constant<int, 8>{});
+        switch (len) {
+            case 7: tail(std::integral_constant<int, 7>{}); break;
+            case 5: tail(std::integral_constant<int, 5>{}); break;
+            case 3: tail(std::integral_constant<int, 3>{}); break;
+            case 1: tail(std::integral_constant<int, 1>{}); break;
+            default: break;
+        }
+        return;
+    }
+    if constexpr (!kSlide) {
+#pragma unroll 1
+        for (; len >= 8; len -= 8, t += 8, wp += 8) run(std::integral_constant<int, 8>{});
+    }
     switch (len) {
         case 7: run(std::integral_constant<int, 7>{}); break;
         case 5: run(std::integral_constant<int, 5>{}); break;
@@ -333,6 +396,7 @@ struct SmemLayout {
     int tile_pitch, tile_w, tile_h, hs_pitch, w_pitch, group_stride;
 };
 
+// lut_n: entries of the table as replicated into shared memory (kLutPremul: rows x entries per row)
 __host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, int lut_n, int lut_kind, int n_groups) {
     SmemLayout L;
     const int k = 2 * radius + 1;
@@ -420,7 +484,8 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
     const int k = 2 * radius + 1;
     const int n_groups = blockDim.x / kThreads;
     const int group = threadIdx.x / kThreads;  // warp group: its own tile buffer, named barrier and tile sequence
-    const SmemLayout L = make_layout(MODE, P, radius, a.lut_n, LK, n_groups);
+    const int lut_total = a.lut_n * a.lut_rows;   // lut_rows = 1 unless LK == kLutPremul
+    const SmemLayout L = make_layout(MODE, P, radius, lut_total, LK, n_groups);
     float* const lut_s = reinterpret_cast<float*>(smem + L.lut_off);
     float* const w_s = reinterpret_cast<float*>(smem + L.w_off);
     int* const hw_s = reinterpret_cast<int*>(smem + L.hw_off);
@@ -436,9 +501,9 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
 
     // one-time per CTA (shared by all groups): replicated LUT, spatial weight rows, half widths
     if constexpr (MODE == kBF)
-        fill_tables_call<LK>(a.lut, a.lut_n, a.w_rows, a.hw, k, lut_s, w_s, hw_s, k * L.w_pitch);
+        fill_tables_call<LK>(a.lut, lut_total, a.w_rows, a.hw, k, lut_s, w_s, hw_s, k * L.w_pitch);
     else
-        fill_tables<LK>(a.lut, a.lut_n, a.w_rows, a.hw, k, lut_s, w_s, hw_s, k * L.w_pitch);
+        fill_tables<LK>(a.lut, lut_total, a.w_rows, a.hw, k, lut_s, w_s, hw_s, k * L.w_pitch);
     constexpr int kRepLog2 = lut_shift(LK) - 2;  // copies per entry (log2)
     if (threadIdx.x == 0) sched[0] = 0;
     // Programmatic dependent launch: the prologue above touches only this filter's constant tables, so it may run while
@@ -762,9 +827,9 @@ cudaError_t launch_tiled(const StencilArgs& a, int sm_count, cudaStream_t stream
     if constexpr (!PEER && MODE != kJBF) {
         if (a.above || a.below) return launch_tiled<MODE, LK, true>(a, sm_count, stream);
     }
-    const int n_groups = groups_that_fit(MODE, a.radius, a.lut_n, LK);
+    const int n_groups = groups_that_fit(MODE, a.radius, a.lut_n * a.lut_rows, LK);
     if (n_groups < 1) return cudaErrorInvalidConfiguration;  // stencil_pick_lut never hands out such a table
-    const SmemLayout L = make_layout(MODE, P, a.radius, a.lut_n, LK, n_groups);
+    const SmemLayout L = make_layout(MODE, P, a.radius, a.lut_n * a.lut_rows, LK, n_groups);
     auto kern = stencil_kernel<MODE, P, LK, PEER>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total);
     if (e != cudaSuccess) return e;
@@ -784,6 +849,9 @@ cudaError_t launch_tiled_kind(const StencilArgs& a, int sm_count, cudaStream_t s
     switch (a.lut_kind) {
         case kLutFull: return launch_tiled<MODE, kLutFull>(a, sm_count, stream);
         case kLutClamp: return launch_tiled<MODE, kLutClamp>(a, sm_count, stream);
+        case kLutPremul:
+            if constexpr (MODE != kABF) return launch_tiled<MODE, kLutPremul>(a, sm_count, stream);
+            return cudaErrorInvalidConfiguration;   // stencil_pick_lut never picks it for ABF
         default: return launch_tiled<MODE, kLutNarrow>(a, sm_count, stream);
     }
 }
@@ -803,8 +871,9 @@ int stencil_max_tiled_radius() { return kMaxTiledRadius; }
 
 int stencil_w_pitch(int radius) { return (2 * radius + 1 + 7) & ~7; }
 
-void stencil_describe(StencilMode mode, int radius, int lut_n, int lut_kind, int* copies, int* clamped, int* groups,
-                      int* smem_bytes) {
+void stencil_describe(StencilMode mode, int radius, int lut_n, int lut_rows, int lut_kind, int* copies, int* clamped,
+                      int* groups, int* smem_bytes) {
+    lut_n *= lut_rows;
     const int g = groups_that_fit(mode, radius, lut_n, lut_kind);
     *copies = 1 << (lut_shift(lut_kind) - 2);
     *clamped = lut_clamped(lut_kind) ? 1 : 0;
@@ -812,7 +881,7 @@ void stencil_describe(StencilMode mode, int radius, int lut_n, int lut_kind, int
     *smem_bytes = g > 0 ? make_layout(mode, outputs_per_thread(mode), radius, lut_n, lut_kind, g).total : 0;
 }
 
-void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, int* lut_n, int* lut_kind) {
+void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, int n_ks, int* lut_n, int* lut_kind) {
     // The table is shared by the warp groups of the one CTA an SM runs.  Candidates, in order of preference at an equal
     // number of warp groups: the whole table 32x replicated (no clamp instruction); the table cut after its last
     // non-zero entry -- every index > last_nz has weight exactly 0, so clamping the index to last_nz+1 (a zero entry)
@@ -832,8 +901,22 @@ void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, 
         *lut_kind = kLutClamp;
     }
     if (g_narrow > best) {
+        best = g_narrow;
         *lut_n = cut_n;
         *lut_kind = kLutNarrow;
+    }
+    // One premultiplied row per distinct spatial weight (n_ks of them) removes the FMUL of every tap (8.5 -> 7.7
+    // instructions per tap for the texture filter's 17 x 17 joint bilateral step, bit-exact).  Measured on B200
+    // (profiles/r02b_premul_ab.txt): 0.559 vs 0.562 ms -- nothing, for the reason given at do_row -- so it is OFF unless
+    // VIP_STENCIL_PREMUL=1 asks for it; it then is taken whenever it keeps as many warp groups as the best plain layout.
+    static const bool premul_on = [] {
+        const char* v = std::getenv("VIP_STENCIL_PREMUL");
+        return v && v[0] == '1';
+    }();
+    if (premul_on && mode != kABF && n_ks > 0 && static_cast<long long>(cut_n) * n_ks <= 16384 &&
+        groups_that_fit(mode, radius, cut_n * n_ks, kLutPremul) >= best) {
+        *lut_n = cut_n;
+        *lut_kind = kLutPremul;
     }
 }
 

@@ -62,6 +62,7 @@ struct StencilArgs {
     const float* lut;           // device: colour table (768 or 1536 floats)
     int lut_n;                  // entries replicated into shared memory
     int lut_kind;               // LutKind of stencil.cu: replication of the table and whether the index is clamped to lut_n-1
+    int lut_rows;               // 1; kLutPremul: rows of the premultiplied table (distinct spatial weights), lut = [lut_rows][lut_n]
     const int* hw;              // device: 2r+1 half widths, hw[ky+r] = floor(sqrt(r^2-ky^2))
     const float* ks_full;       // device: ksize*ksize spatial kernel (the generic large-radius kernel reads it)
     const float* w_rows;        // device: ksize rows of stencil_w_pitch(radius) floats: row ky = its 2*hw+1 non-zero weights from index 0, zero padded
@@ -76,12 +77,14 @@ cudaError_t launch_stencil(StencilMode mode, const StencilArgs& a, int sm_count,
 // Largest radius the tiled kernels cover; beyond it the generic one-thread-per-pixel kernel runs.
 int stencil_max_tiled_radius();
 // Launch configuration of the tiled kernels for a table of `lut_n` entries of kind `lut_kind` (host logic only).
-void stencil_describe(StencilMode mode, int radius, int lut_n, int lut_kind, int* copies, int* clamped, int* groups,
-                      int* smem_bytes);
+void stencil_describe(StencilMode mode, int radius, int lut_n, int lut_rows, int lut_kind, int* copies, int* clamped,
+                      int* groups, int* smem_bytes);
 // Floats per row of StencilArgs::w_rows.
 int stencil_w_pitch(int radius);
 // Decides how many colour-table entries are replicated in shared memory and whether the index is clamped.
-void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, int* lut_n, int* lut_kind);
+// n_ks: distinct non-zero values of the spatial kernel (rows a premultiplied table would need).
+void stencil_pick_lut(StencilMode mode, int radius, int table_len, int last_nz, int n_ks, int* lut_n, int* lut_kind);
+constexpr int kStencilLutPremul = 3;   // LutKind kLutPremul
 
 // gradient.cu
 cudaError_t launch_gradient_u8(const std::uint8_t* src, float* dst, int width, int height, int channels, int src_y0,

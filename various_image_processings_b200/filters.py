@@ -236,6 +236,10 @@ class CudaBilateralTextureFilter:
     def execute_async(self, d_src, d_dst, stream=None):
         check(lib().vip_btf_run(self._h, _ptr(d_src), _ptr(d_dst), _stream(stream)), "vip_btf_run")
 
+    def set_graph(self, on=True):
+        """Replay a run's 3 x nitr launches as one captured CUDA graph per (src, dst) pair (non-default streams only)."""
+        check(lib().vip_btf_set_graph(self._h, int(bool(on))), "vip_btf_set_graph")
+
     def compute_blur_and_rtv(self, d_image, d_magnitude, d_blurred, d_rtv, stream=None):
         check(lib().vip_btf_blur_rtv(self._h, _ptr(d_image), _ptr(d_magnitude), _ptr(d_blurred), _ptr(d_rtv),
                                      _stream(stream)), "vip_btf_blur_rtv")
