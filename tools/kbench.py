@@ -115,4 +115,8 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if os.environ.get("KB_STREAM", "0") == "1":      # a non-default stream (CUDA-graph replay needs one)
+        with torch.cuda.stream(torch.cuda.Stream()):
+            main()
+    else:
+        main()

@@ -78,7 +78,19 @@ def main():
                           "note": "pinned host buffers, H2D + kernels + D2H, two streams per device"}), flush=True)
         del mg
     print(json.dumps({"workload": "stream_1080p_all_three", "n_gpus": args.gpus, "frames": nf, "seconds": total,
-                      "frames_per_s": nf / total, "mpixel_per_s": nf * w * h / total / 1e6}), flush=True)
+                      "frames_per_s": nf / total, "mpixel_per_s": nf * w * h / total / 1e6,
+                      "note": "three passes over the host frames, one filter kind per pass (round-1 path)"}), flush=True)
+    # configs[4] as one pass: every frame uploaded ONCE and sent through all three filters (vip_mg_run_batch_set_host)
+    out2, out3 = vip.PinnedBuffer(nf * w * h * 3), vip.PinnedBuffer(nf * w * h * 3)   # kept alive: .array is only a view
+    outs = {"bf": out.array, "abf": out2.array, "btf": out3.array}
+    mg = vip.MultiGpuFilter(devs, "bf", w, h, ksize=9, nitr=3)
+    mg.execute_batch_set(frames.array, outs, min(nf, 4 * args.gpus))   # warm-up
+    t0 = time.perf_counter()
+    mg.execute_batch_set(frames.array, outs, nf)
+    dt = time.perf_counter() - t0
+    print(json.dumps({"workload": "stream_1080p_filter_set", "n_gpus": args.gpus, "frames": nf, "seconds": dt,
+                      "frames_per_s": nf / dt, "mpixel_per_s": nf * w * h / dt / 1e6, "peer_access": mg.peer_access(),
+                      "note": "one upload per frame, BF + ABF + BTF, three downloads, one host thread per device"}), flush=True)
 
 
 if __name__ == "__main__":

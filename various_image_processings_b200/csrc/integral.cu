@@ -6,21 +6,26 @@
 // SURVEY.md 8a/a11).  Float sources accumulate in fp32 (the reference's own test allows 1 % there,
 // test/border_replicated_integral_image.cpp:36-39).
 //
-// The stage is HBM-bound: 12 B written + C bytes read per padded cell is the floor.  Three launches:
+// The stage is HBM-bound: 12 B written + C bytes read per padded cell is the floor.  Every (8-row, 256-column) tile of the
+// table is produced independently from three small sets of aggregates -- four launches, all but the last tiny:
 //  K1 band sums   32-row bands x 256-column chunks, one thread per padded column: vertical sums of the clamped source,
-//                 written at every 8th row (the running sum inside the band) plus the band total;
+//                 written at every 8th row (the running sum inside the band) plus the band total; the same pass reduces
+//                 every row of the chunk to its ROW SUM (one warp reduction per row and channel);
 //  K2 band scan   exclusive prefix of the band totals over the bands (tiny: th/32 entries per column);
-//  K3 scan+store  one CTA per 8-row band walks along the row in 256-column chunks.  Phase A: a thread per column
-//                 turns the 8 source rows into vertical prefix sums (start value from K1/K2) in shared memory;
-//                 phase B: a WARP per row, a lane per 8 adjacent columns: lane-local prefix, then one
-//                 __shfl_up_sync inclusive scan of the lane totals and a register carry along the row -- no block
-//                 barrier inside the scan; phase C: fully coalesced 128-byte stores of the finished chunk.
+//  K2b row carry  for every chunk k and row Y: the table value just left of the chunk, T(Y, 256 k - 1) = the sum over all
+//                 rows <= Y of the row sums of the chunks left of k -- one block scan per (chunk, channel) over th rows;
+//  K3 scan+store  one CTA per tile.  Phase A: a thread per column turns the 8 source rows into vertical prefix sums
+//                 (start value from K1/K2) in shared memory; phase B: a WARP per row, a lane per 8 adjacent columns:
+//                 lane-local prefix, one __shfl_up_sync scan of the lane totals, plus the row's carry from K2b;
+//                 phase C: fully coalesced 128-byte stores.  (Round 1 let one CTA walk along a whole 8-row band with a
+//                 running carry: 272 CTAs at 4K, 23 % occupancy, 49 us of the 77; tiles are 16x as many CTAs.)
 // Traffic: the source is read twice (the second time from L2 for anything up to 8K), the table written once; the
-// K1/K2 arrays are 1/8 of the table and stay in L2.
+// aggregate arrays are 1/8 of the table and stay in L2.
 #include <cuda_runtime.h>
 
 #include <cstdint>
 #include <mutex>
+#include <type_traits>
 
 #include "vip_internal.h"
 
@@ -52,41 +57,118 @@ __device__ __forceinline__ const S* cell_ptr(const S* __restrict__ src, const in
     return src + (static_cast<size_t>(sy) * W + sx) * C;
 }
 
-// K1: sub[(Y/8)][X][c] = sum of padded rows [32*band, Y) of column X (Y a multiple of 8); tot[band][X][c] = band total
+template <typename A>
+__device__ __forceinline__ A warp_sum(A v) {
+    if constexpr (std::is_same<A, std::uint32_t>::value) {
+        return __reduce_add_sync(0xffffffffu, v);   // REDUX: one instruction
+    } else {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+        return v;
+    }
+}
+
+// K1: sub[(Y/8)][X][c] = sum of padded rows [32*band, Y) of column X (Y a multiple of 8); tot[band][X][c] = band total;
+// rowsum[(chunk*C + c)*th + Y] = sum of the cells of padded row Y inside this CTA's 256 columns
 template <typename S, int C>
 __global__ void __launch_bounds__(kScanThreads) integral_bands_kernel(const S* __restrict__ src,
                                                                      typename AccOf<S>::type* __restrict__ sub,
                                                                      typename AccOf<S>::type* __restrict__ tot,
+                                                                     typename AccOf<S>::type* __restrict__ rowsum,
                                                                      const int W, const int H, const int r) {
     using A = typename AccOf<S>::type;
+    __shared__ A part[kScanThreads / 32][kBandRows][C];   // per-warp row sums, added in a fixed order (deterministic for float)
     const int tw = W + 2 * r + 1, th = H + 2 * r + 1;
     const int X = blockIdx.x * kScanThreads + threadIdx.x;
-    if (X >= tw) return;
+    const bool in = X < tw;
     const int band = blockIdx.y;
     const int Y0 = band * kBandRows;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane < kBandRows) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) part[warp][lane][c] = A(0);   // rows past the table's end stay zero
+    }
+    __syncwarp();
     A acc[C];
 #pragma unroll
     for (int c = 0; c < C; ++c) acc[c] = A(0);
 #pragma unroll
     for (int q = 0; q < kSubPerBand; ++q) {
         const int Ys = Y0 + q * kSubRows;
-        if (Ys >= th) break;
-        A* o = sub + (static_cast<size_t>(Ys / kSubRows) * tw + X) * C;
+        if (Ys >= th) break;   // uniform over the CTA
+        if (in) {
+            A* o = sub + (static_cast<size_t>(Ys / kSubRows) * tw + X) * C;
 #pragma unroll
-        for (int c = 0; c < C; ++c) o[c] = acc[c];
+            for (int c = 0; c < C; ++c) o[c] = acc[c];
+        }
+        S pix[kSubRows][C];
 #pragma unroll
         for (int j = 0; j < kSubRows; ++j) {
             const int Y = Ys + j;
-            if (Y >= 1 && Y < th && X >= 1) {
-                const S* p = cell_ptr<S, C>(src, W, H, r, Y, X);
+            const bool ok = in && Y >= 1 && Y < th && X >= 1;
+            const S* p = cell_ptr<S, C>(src, W, H, r, ok ? Y : 1, ok ? X : 1);
 #pragma unroll
-                for (int c = 0; c < C; ++c) acc[c] += static_cast<A>(__ldg(p + c));
+            for (int c = 0; c < C; ++c) pix[j][c] = ok ? __ldg(p + c) : S(0);
+        }
+#pragma unroll
+        for (int j = 0; j < kSubRows; ++j) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                const A v = static_cast<A>(pix[j][c]);
+                acc[c] += v;
+                const A rs = warp_sum<A>(v);
+                if (lane == 0) part[warp][q * kSubRows + j][c] = rs;
             }
         }
     }
-    A* t = tot + (static_cast<size_t>(band) * tw + X) * C;
+    if (in) {
+        A* t = tot + (static_cast<size_t>(band) * tw + X) * C;
 #pragma unroll
-    for (int c = 0; c < C; ++c) t[c] = acc[c];
+        for (int c = 0; c < C; ++c) t[c] = acc[c];
+    }
+    __syncthreads();
+    if (threadIdx.x < kBandRows * C) {
+        const int row = threadIdx.x / C, c = threadIdx.x - row * C;
+        const int Y = Y0 + row;
+        A sum = A(0);
+#pragma unroll
+        for (int w = 0; w < kScanThreads / 32; ++w) sum += part[w][row][c];
+        if (Y < th) rowsum[(static_cast<size_t>(blockIdx.x) * C + c) * th + Y] = sum;
+    }
+}
+
+// K2b: carry[(k*C + c)*th + Y] = sum over rows Y' <= Y of the row sums of the chunks k' < k: the table value just left of
+// chunk k in row Y.  One CTA per (chunk k >= 1, channel): an inclusive block scan over the th rows.
+constexpr int kCarryThreads = 1024;
+template <typename A>
+__global__ void __launch_bounds__(kCarryThreads) integral_row_carry_kernel(const A* __restrict__ rowsum, A* __restrict__ carry,
+                                                                           const int th, const int C) {
+    __shared__ A warp_tot[kCarryThreads / 32];
+    __shared__ A run_s;
+    const int k = blockIdx.x + 1, c = blockIdx.y;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) run_s = A(0);
+    __syncthreads();
+    for (int base = 0; base < th; base += kCarryThreads) {
+        const int Y = base + tid;
+        A v = A(0);
+        if (Y < th)
+            for (int kk = 0; kk < k; ++kk) v += __ldg(rowsum + (static_cast<size_t>(kk) * C + c) * th + Y);
+        A incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const A up = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += up;
+        }
+        if (lane == 31) warp_tot[warp] = incl;
+        __syncthreads();
+        A before = run_s;
+        for (int q = 0; q < warp; ++q) before += warp_tot[q];
+        if (Y < th) carry[(static_cast<size_t>(k) * C + c) * th + Y] = incl + before;
+        __syncthreads();
+        if (tid == kCarryThreads - 1) run_s = incl + before;
+        __syncthreads();
+    }
 }
 
 // K2: in-place exclusive scan of tot over the bands.  A CTA owns 32 (column, channel) entries; its 8 warps split the
@@ -130,12 +212,13 @@ __global__ void __launch_bounds__(kScanThreads) integral_band_scan_kernel(A* __r
     }
 }
 
-// K3: scan + store (see the header).  S holds the chunk as [row][pad(column*C + channel)], one spare word after every
-// 8*C so that the 32 lanes of phase B start in 32 different banks.
+// K3: scan + store of one (8-row, 256-column) tile (see the header).  Sm holds the tile as [row][pad(column*C + channel)],
+// one spare word after every 8*C so that the 32 lanes of phase B start in 32 different banks.
 template <typename S, int C>
 __global__ void __launch_bounds__(kScanThreads) integral_scan_kernel(const S* __restrict__ src,
                                                                     const typename AccOf<S>::type* __restrict__ sub,
                                                                     const typename AccOf<S>::type* __restrict__ tot,
+                                                                    const typename AccOf<S>::type* __restrict__ carry_in,
                                                                     typename AccOf<S>::type* __restrict__ table,
                                                                     const int W, const int H, const int r) {
     using A = typename AccOf<S>::type;
@@ -143,24 +226,26 @@ __global__ void __launch_bounds__(kScanThreads) integral_scan_kernel(const S* __
     constexpr int kRowWords = kChunk * C + kChunk / 8;
     __shared__ A Sm[kSubRows][kRowWords];
     const int tw = W + 2 * r + 1, th = H + 2 * r + 1;
-    const int b8 = blockIdx.x, Y0 = b8 * kSubRows;
+    const int chunk = blockIdx.x, X0 = chunk * kChunk;
+    const int b8 = blockIdx.y, Y0 = b8 * kSubRows;
     const int band = Y0 / kBandRows;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    S pix[kSubRows][C];
-    A start[C];
-    auto prefetch = [&](const int X0) {
+    // phase A: vertical prefix of this thread's column, starting from the sum of everything above the tile
+    {
         const int X = X0 + tid;
         const bool in = X >= 1 && X < tw;
+        A acc[C];
 #pragma unroll
-        for (int c = 0; c < C; ++c) start[c] = A(0);
+        for (int c = 0; c < C; ++c) acc[c] = A(0);
         if (in) {
             const A* t = tot + (static_cast<size_t>(band) * tw + X) * C;
             const A* u = sub + (static_cast<size_t>(b8) * tw + X) * C;
 #pragma unroll
-            for (int c = 0; c < C; ++c) start[c] = __ldg(t + c) + __ldg(u + c);
+            for (int c = 0; c < C; ++c) acc[c] = __ldg(t + c) + __ldg(u + c);
         }
         const S* const colp = src + static_cast<size_t>(clampi(X - 1 - r, 0, W - 1)) * C;
+        S pix[kSubRows][C];
 #pragma unroll
         for (int j = 0; j < kSubRows; ++j) {
             const int Y = Y0 + j;
@@ -169,78 +254,63 @@ __global__ void __launch_bounds__(kScanThreads) integral_scan_kernel(const S* __
 #pragma unroll
             for (int c = 0; c < C; ++c) pix[j][c] = ok ? __ldg(p + c) : S(0);
         }
-    };
-
-    A carry[C];
+        const int w0 = tid * C + tid / 8;
 #pragma unroll
-    for (int c = 0; c < C; ++c) carry[c] = A(0);
-    prefetch(0);
-    for (int X0 = 0; X0 < tw; X0 += kChunk) {
-        // phase A: vertical prefix of this thread's column
-        {
-            A acc[C];
-#pragma unroll
-            for (int c = 0; c < C; ++c) acc[c] = start[c];
-            const int w0 = tid * C + tid / 8;
-#pragma unroll
-            for (int j = 0; j < kSubRows; ++j) {
-#pragma unroll
-                for (int c = 0; c < C; ++c) {
-                    acc[c] += static_cast<A>(pix[j][c]);
-                    Sm[j][w0 + c] = acc[c];
-                }
-            }
-        }
-        __syncthreads();
-        if (X0 + kChunk < tw) prefetch(X0 + kChunk);  // in flight during phases B and C
-        // phase B: warp = row, lane = 8 adjacent columns
-        {
-            A* row = &Sm[warp][lane * (kLaneWords + 1)];
-            A v[8][C], run[C];
-#pragma unroll
-            for (int c = 0; c < C; ++c) run[c] = A(0);
-#pragma unroll
-            for (int m = 0; m < 8; ++m) {
-#pragma unroll
-                for (int c = 0; c < C; ++c) {
-                    run[c] += row[m * C + c];
-                    v[m][c] = run[c];
-                }
-            }
+        for (int j = 0; j < kSubRows; ++j) {
 #pragma unroll
             for (int c = 0; c < C; ++c) {
-                A incl = run[c];
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const A up = __shfl_up_sync(0xffffffffu, incl, d);
-                    if (lane >= d) incl += up;
-                }
-                A excl = __shfl_up_sync(0xffffffffu, incl, 1);
-                if (lane == 0) excl = A(0);
-                excl += carry[c];
-                carry[c] += __shfl_sync(0xffffffffu, incl, 31);
-#pragma unroll
-                for (int m = 0; m < 8; ++m) row[m * C + c] = v[m][c] + excl;
+                acc[c] += static_cast<A>(pix[j][c]);
+                Sm[j][w0 + c] = acc[c];
             }
         }
-        __syncthreads();
-        // phase C: coalesced stores
-        {
-            const int nwords = min(kChunk, tw - X0) * C;
-            const int nrows = min(kSubRows, th - Y0);
-            A* const tbase = table + (static_cast<size_t>(Y0) * tw + X0) * C;
+    }
+    __syncthreads();
+    // phase B: warp = row, lane = 8 adjacent columns; the row starts from the table value just left of the chunk
+    {
+        const int Y = Y0 + warp;
+        A* row = &Sm[warp][lane * (kLaneWords + 1)];
+        A v[8][C], run[C];
 #pragma unroll
-            for (int q = 0; q < C; ++q) {
-                const int i = tid + q * kScanThreads;
-                if (i < nwords) {
-                    const int si = i + i / kLaneWords;
+        for (int c = 0; c < C; ++c) run[c] = A(0);
 #pragma unroll
-                    for (int j = 0; j < kSubRows; ++j)
-                        if (j < nrows) tbase[static_cast<size_t>(j) * tw * C + i] = Sm[j][si];
-                }
+        for (int m = 0; m < 8; ++m) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                run[c] += row[m * C + c];
+                v[m][c] = run[c];
             }
         }
-        __syncthreads();
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            A incl = run[c];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const A up = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += up;
+            }
+            A excl = __shfl_up_sync(0xffffffffu, incl, 1);
+            if (lane == 0) excl = A(0);
+            if (chunk > 0 && Y < th) excl += __ldg(carry_in + (static_cast<size_t>(chunk) * C + c) * th + Y);
+#pragma unroll
+            for (int m = 0; m < 8; ++m) row[m * C + c] = v[m][c] + excl;
+        }
+    }
+    __syncthreads();
+    // phase C: coalesced stores
+    {
+        const int nwords = min(kChunk, tw - X0) * C;
+        const int nrows = min(kSubRows, th - Y0);
+        A* const tbase = table + (static_cast<size_t>(Y0) * tw + X0) * C;
+#pragma unroll
+        for (int q = 0; q < C; ++q) {
+            const int i = tid + q * kScanThreads;
+            if (i < nwords) {
+                const int si = i + i / kLaneWords;
+#pragma unroll
+                for (int j = 0; j < kSubRows; ++j)
+                    if (j < nrows) tbase[static_cast<size_t>(j) * tw * C + i] = Sm[j][si];
+            }
+        }
     }
 }
 
@@ -277,18 +347,25 @@ cudaError_t launch_integral_t(const S* src, typename AccOf<S>::type* table, int 
     using A = typename AccOf<S>::type;
     const int tw = width + 2 * radius + 1, th = height + 2 * radius + 1;
     const int nsub = (th + kSubRows - 1) / kSubRows, nbands = (th + kBandRows - 1) / kBandRows;
+    const int nchunks = (tw + kChunk - 1) / kChunk;
     const size_t row_elems = static_cast<size_t>(tw) * C;
+    const size_t rs_elems = static_cast<size_t>(nchunks) * C * th;   // row sums and row carries: [chunk][channel][row]
     A* aux = nullptr;
-    cudaError_t e = scratch_alloc(reinterpret_cast<void**>(&aux), (nsub + nbands) * row_elems * sizeof(A), stream);
+    cudaError_t e = scratch_alloc(reinterpret_cast<void**>(&aux), ((nsub + nbands) * row_elems + 2 * rs_elems) * sizeof(A), stream);
     if (e != cudaSuccess) return e;
     A* sub = aux;
     A* tot = aux + nsub * row_elems;
-    const dim3 g1((tw + kScanThreads - 1) / kScanThreads, nbands);
-    integral_bands_kernel<S, C><<<g1, kScanThreads, 0, stream>>>(src, sub, tot, width, height, radius);
+    A* rowsum = tot + nbands * row_elems;
+    A* carry = rowsum + rs_elems;
+    const dim3 g1(nchunks, nbands);
+    integral_bands_kernel<S, C><<<g1, kScanThreads, 0, stream>>>(src, sub, tot, rowsum, width, height, radius);
     integral_band_scan_kernel<A><<<(static_cast<int>(row_elems) + 31) / 32, kScanThreads, 0, stream>>>(
         tot, static_cast<int>(row_elems), nbands);
-    integral_scan_kernel<S, C><<<nsub, kScanThreads, 0, stream>>>(src, sub, tot, table, width, height, radius);
-    count_launch(3);
+    if (nchunks > 1)
+        integral_row_carry_kernel<A><<<dim3(nchunks - 1, C), kCarryThreads, 0, stream>>>(rowsum, carry, th, C);
+    integral_scan_kernel<S, C><<<dim3(nchunks, nsub), kScanThreads, 0, stream>>>(src, sub, tot, carry, table, width, height,
+                                                                                  radius);
+    count_launch(nchunks > 1 ? 4 : 3);
     e = cudaGetLastError();
     cudaFreeAsync(aux, stream);
     return e;
