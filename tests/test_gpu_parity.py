@@ -118,7 +118,8 @@ def test_lenna_crop_abf_btf(vip):
     # the guide stage evaluates expf on the device (CUDA libdevice); vs the glibc-expf oracle a guide pixel can differ by
     # one level on a natural image and three iterations spread it: bounded here, exact vs the reference's own CUDA kernels
     want = O.o_btf(crop, 9, 3)
-    assert (got != want).mean() < 2e-3 and maxdiff(got, want) <= 2
+    # (measured: 11 of 196 608 samples, all by one level)
+    assert (got != want).mean() < 2e-4 and maxdiff(got, want) <= 1
     if O.have_ref_cuda():
         R = O.ref_cuda()
         d_src = dev(crop)
@@ -296,8 +297,10 @@ def test_btf_end_to_end(vip, w, h, k, nitr):
     if (w, h, k, nitr) == (64, 48, 9, 3):
         # vs the reference CPU pipeline (own JBF substituted for ximgproc): the argmin can move on
         # isolated pixels (float vs double epsilon), so report rather than bound tightly
+        # (measured on B200, tools/btf_bounds_probe.py: no sample differs on this fixture; BASELINE.md 2b has the table for
+        # the content classes where samples do move)
         d = np.abs(got.astype(int) - G["btf_k9_n3_smooth_cpu"].astype(int))
-        assert (d > 1).mean() < 0.02, f"{(d > 1).mean():.4f} of samples differ by more than 1 LSB from the CPU reference"
+        assert d.max() <= 1 and (d > 0).mean() < 1e-3, f"max {d.max()}, {(d > 0).mean():.5f} of samples differ from the CPU reference"
 
 
 @pytest.mark.parametrize("off", [1, 2, 3])
@@ -967,3 +970,25 @@ def test_btf_graph_replay_is_identical(vip):
             f.execute_async(d_src, d_dst, stream=st)
             st.synchronize()
             assert np.array_equal(d_dst.cpu().numpy(), want), f"seed {seed} rep {rep}"
+
+
+def test_tma_tile_staging_is_identical(vip):
+    """VIP_STENCIL_TMA=1 (read once per process, hence a subprocess): interior tiles of the bilateral kernel are staged by
+    bulk asynchronous copies (TMA) + a repack from shared memory instead of aligned 32-bit global loads.  Same bytes out."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = r'''
+import sys, numpy as np, torch
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+import _oracle as O, various_image_processings_b200 as vip
+for (w, h, k) in ((256, 96, 9), (512, 200, 11), (1024, 70, 31), (320, 64, 5), (208, 130, 21)):
+    img = O.rand_image(w, h, seed=w + k)
+    d_src = torch.from_numpy(img).cuda(); d_dst = torch.empty_like(d_src)
+    vip.CudaBilateralFilter(w, h, k).bilateral_filter(d_src, d_dst)
+    assert np.array_equal(d_dst.cpu().numpy(), O.o_bf(img, k)), (w, h, k)
+print("tma ok")
+''' % (root, os.path.join(root, "tests"))
+    env = dict(os.environ, VIP_STENCIL_TMA="1")
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env)
+    assert p.returncode == 0 and "tma ok" in p.stdout, p.stderr[-2000:]

@@ -152,8 +152,10 @@ __global__ void __launch_bounds__(kCarryThreads) integral_row_carry_kernel(const
     for (int base = 0; base < th; base += kCarryThreads) {
         const int Y = base + tid;
         A v = A(0);
-        if (Y < th)
-            for (int kk = 0; kk < k; ++kk) v += __ldg(rowsum + (static_cast<size_t>(kk) * C + c) * th + Y);
+        if (Y < th) {
+#pragma unroll 8
+            for (int kk = 0; kk < k; ++kk) v += __ldg(rowsum + (static_cast<size_t>(kk) * C + c) * th + Y);   // independent loads
+        }
         A incl = v;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {

@@ -40,7 +40,12 @@ namespace {
 
 constexpr int kThreads = 256;            // threads of one warp group (one tile in flight per group)
 constexpr int kWarps = kThreads / 32;
-constexpr int kMaxGroups = 3;            // warp groups per CTA: 24 warps / SM, <= 80 registers per thread
+constexpr int kMaxGroups = 4;            // most warp groups any mode runs per CTA (scheduler slots, mbarriers)
+// Warp groups per CTA and hence registers per thread (one CTA per SM): BF / JBF 3 groups = 24 warps at <= 80 registers;
+// ABF 4 groups = 32 warps at <= 64 registers.  Measured on B200 (profiles/r02f_groups_ab.txt, all bit-exact): 4 groups
+// make ABF 4K r=7 1.4 % faster (0.794 -> 0.783 ms) but BF 8K r=15 4 % slower (6.855 -> 7.142 ms; the 64-register run
+// body needs 4.5 % more instructions) and JBF 1 % slower.
+__host__ __device__ constexpr int max_groups(const int mode) { return mode == kABF ? 4 : 3; }
 constexpr int kSmemBudget = 232448 - 1024;  // opt-in maximum of dynamic shared memory per CTA (227 KB) minus the driver's 1 KB
 constexpr int kTileRows = 32;  // one lane per output row
 constexpr int kMaxTiledRadius = 15;
@@ -113,6 +118,49 @@ __device__ __forceinline__ void load_packed4(const std::uint8_t* __restrict__ p,
     const std::uint32_t* w = reinterpret_cast<const std::uint32_t*>(p - m);
     const std::uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
     const std::uint32_t w3 = m ? __ldg(w + 3) : 0u;
+    const unsigned sh = 8u * m;
+    const std::uint32_t v0 = __funnelshift_r(w0, w1, sh), v1 = __funnelshift_r(w1, w2, sh), v2 = __funnelshift_r(w2, w3, sh);
+    out[0] = v0 & 0x00ffffffu;
+    out[1] = __funnelshift_r(v0, v1, 24) & 0x00ffffffu;
+    out[2] = __funnelshift_r(v1, v2, 16) & 0x00ffffffu;
+    out[3] = v2 >> 8;
+}
+
+// ---- TMA (bulk asynchronous copy) tile staging, BF only, opt-in (VIP_STENCIL_TMA=1; DESIGN.md 3.3 has the A/B) ----------
+// One bulk copy per tile row moves the row's raw bytes (16-byte aligned superset) global -> shared through the TMA unit,
+// completion counted on an mbarrier; the group then repacks bytes -> 32-bit pixels from shared memory.
+__device__ __forceinline__ void mbar_init(const std::uint32_t mbar, const int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(const std::uint32_t mbar, const std::uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(const std::uint32_t mbar, const std::uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "DONE:\n\t}" ::"r"(mbar),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(const std::uint32_t smem_dst, const void* gmem_src, const std::uint32_t bytes,
+                                         const std::uint32_t mbar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_dst),
+                 "l"(gmem_src), "r"(bytes), "r"(mbar)
+                 : "memory");
+}
+// Four packed BGR pixels (12 bytes at any byte offset) from SHARED memory: the twin of load_packed4
+__device__ __forceinline__ void load_packed4_shared(const std::uint32_t addr, std::uint32_t out[4]) {
+    const unsigned m = addr & 3u;
+    const std::uint32_t a0 = addr - m;
+    std::uint32_t w0, w1, w2, w3 = 0u;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w0) : "r"(a0));
+    asm volatile("ld.shared.u32 %0, [%1+4];" : "=r"(w1) : "r"(a0));
+    asm volatile("ld.shared.u32 %0, [%1+8];" : "=r"(w2) : "r"(a0));
+    if (m) asm volatile("ld.shared.u32 %0, [%1+12];" : "=r"(w3) : "r"(a0));
     const unsigned sh = 8u * m;
     const std::uint32_t v0 = __funnelshift_r(w0, w1, sh), v1 = __funnelshift_r(w1, w2, sh), v2 = __funnelshift_r(w2, w3, sh);
     out[0] = v0 & 0x00ffffffu;
@@ -394,10 +442,16 @@ __device__ __forceinline__ void do_row(int len, const typename Elem<MODE>::type*
 struct SmemLayout {
     int lut_off, w_off, hw_off, sched_off, tile_off, hs_off, bs_off, total;   // tile_off / hs_off / bs_off: group 0; group g adds g * group_stride
     int tile_pitch, tile_w, tile_h, hs_pitch, w_pitch, group_stride;
+    int stage_off, stage_pitch, mbar_off;   // TMA staging (BF): raw byte rows of the tile + one mbarrier per group
 };
 
+// Raw-byte staging buffer of the TMA tile load: rows of 3 * tile_w bytes plus up to 15 bytes of alignment lead-in,
+// rounded to the 16 bytes a bulk copy moves
+__host__ __device__ constexpr int stage_pitch_bytes(int P, int radius) { return (3 * (kWarps * P + 2 * radius) + 15 + 15) & ~15; }
+
 // lut_n: entries of the table as replicated into shared memory (kLutPremul: rows x entries per row)
-__host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, int lut_n, int lut_kind, int n_groups) {
+__host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, int lut_n, int lut_kind, int n_groups,
+                                                  bool tma = false) {
     SmemLayout L;
     const int k = 2 * radius + 1;
     L.tile_w = kWarps * P + 2 * radius;
@@ -413,8 +467,11 @@ __host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, i
     L.hw_off = off;
     off += k * 4;
     off = (off + 15) & ~15;
-    L.sched_off = off;  // tile counter of the CTA + the tile each group is working on
-    off += 16;
+    L.sched_off = off;  // tile counter of the CTA + the tile each group is working on (1 + kMaxGroups ints)
+    off += 32;
+    static_assert(1 + kMaxGroups <= 8, "scheduler slots");
+    L.mbar_off = off;   // 8 bytes per group (always reserved: 32 bytes)
+    off += 8 * 4;
     L.tile_off = off;
     off += L.tile_pitch * L.tile_h * (mode == kJBF ? 8 : 4);
     off = (off + 15) & ~15;
@@ -423,6 +480,10 @@ __host__ __device__ inline SmemLayout make_layout(int mode, int P, int radius, i
     off = (off + 15) & ~15;
     L.bs_off = off;  // ABF: k x k box sums of the tile's outputs, uint4 {B, G, R, -} per output
     if (mode == kABF) off += L.hs_pitch * kTileRows * 16;
+    off = (off + 15) & ~15;
+    L.stage_off = off;
+    L.stage_pitch = stage_pitch_bytes(P, radius);
+    if (tma) off += L.stage_pitch * L.tile_h;
     off = (off + 15) & ~15;
     L.group_stride = off - L.tile_off;
     L.total = L.tile_off + n_groups * L.group_stride;
@@ -475,9 +536,10 @@ __device__ __noinline__ void fill_tables_call(const float* __restrict__ lut, con
 // PEER: halo rows that the strip buffer does not hold are staged straight from the neighbouring ranks' device memory
 // (StencilArgs::above / below: peer or IPC-mapped pointers, i.e. NVLink loads inside the tile staging) -- the halo
 // exchange of a row-strip split fused into the filter, no halo copy and no halo rows in the local buffer at all.
-template <int MODE, int P, int LK, bool PEER>
-__global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
+template <int MODE, int P, int LK, bool PEER, bool TMA = false>
+__global__ void __launch_bounds__(kThreads * max_groups(MODE), 1)
     stencil_kernel(const StencilArgs a, const int tiles_x, const int n_tiles) {
+    static_assert(!TMA || (MODE == kBF && !PEER), "TMA staging is built for the plain bilateral kernel only");
     using E = typename Elem<MODE>::type;
     extern __shared__ __align__(16) unsigned char smem[];
     const int radius = a.radius;
@@ -485,7 +547,7 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
     const int n_groups = blockDim.x / kThreads;
     const int group = threadIdx.x / kThreads;  // warp group: its own tile buffer, named barrier and tile sequence
     const int lut_total = a.lut_n * a.lut_rows;   // lut_rows = 1 unless LK == kLutPremul
-    const SmemLayout L = make_layout(MODE, P, radius, lut_total, LK, n_groups);
+    const SmemLayout L = make_layout(MODE, P, radius, lut_total, LK, n_groups, TMA);
     float* const lut_s = reinterpret_cast<float*>(smem + L.lut_off);
     float* const w_s = reinterpret_cast<float*>(smem + L.w_off);
     int* const hw_s = reinterpret_cast<int*>(smem + L.hw_off);
@@ -506,6 +568,17 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
         fill_tables<LK>(a.lut, lut_total, a.w_rows, a.hw, k, lut_s, w_s, hw_s, k * L.w_pitch);
     constexpr int kRepLog2 = lut_shift(LK) - 2;  // copies per entry (log2)
     if (threadIdx.x == 0) sched[0] = 0;
+    [[maybe_unused]] const std::uint32_t mbar =
+        static_cast<std::uint32_t>(__cvta_generic_to_shared(smem + L.mbar_off + 8 * group));
+    [[maybe_unused]] const std::uint32_t stage =
+        static_cast<std::uint32_t>(__cvta_generic_to_shared(smem + L.stage_off + group * L.group_stride));
+    [[maybe_unused]] std::uint32_t tma_phase = 0;
+    if constexpr (TMA) {
+        if (tid == 0) {
+            mbar_init(mbar, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+    }
     // Programmatic dependent launch: the prologue above touches only this filter's constant tables, so it may run while
     // the previous kernel of the stream is still draining; everything below reads / writes images and waits for it.
     // The next kernel may be scheduled as soon as SMs free up (no-ops when launched without the attribute).
@@ -553,7 +626,34 @@ __global__ void __launch_bounds__(kThreads * kMaxGroups, 1)
         // leftover columns go pixel by pixel with clamped coordinates.
         const bool interior = X0 - radius >= 0 && X0 - radius + tw < W;
         const int vec_cols = interior ? (tw & ~3) : 0;
-        if (interior) {
+        if constexpr (TMA) {
+            if (interior) {
+                // the host checked that the image rows start 16-byte aligned: the lead-in only depends on the column
+                const std::uint32_t lead = static_cast<std::uint32_t>((X0 - radius) * 3) & 15u;
+                const std::uint32_t row_bytes = (lead + 3u * tw + 15u) & ~15u;
+                if (warp == 0) {
+                    // the previous tile's repack (generic-proxy reads of the staging rows) is complete (group_sync above);
+                    // order it before the asynchronous-proxy writes of the new copies
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    if (lane == 0) mbar_expect_tx(mbar, row_bytes * th);
+                    __syncwarp();
+                    for (int ey = lane; ey < th; ey += 32)
+                        bulk_g2s(stage + ey * L.stage_pitch, a.src + row_offset(ey) + (X0 - radius) * 3 - lead, row_bytes, mbar);
+                }
+                mbar_wait(mbar, tma_phase);
+                tma_phase ^= 1u;
+                const int gpr = tw >> 2;
+                for (int item = tid; item < th * gpr; item += kThreads) {
+                    const int ey = item / gpr, g = item - ey * gpr;
+                    std::uint32_t v[4];
+                    load_packed4_shared(stage + ey * L.stage_pitch + lead + 12 * g, v);
+                    E* const trow = tile + ey * tp + 4 * g;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) trow[j] = v[j];
+                }
+            }
+        }
+        if (interior && !TMA) {
             const int gpr = tw >> 2;
             for (int item = tid; item < th * gpr; item += kThreads) {
                 const int ey = item / gpr, g = item - ey * gpr;
@@ -816,7 +916,7 @@ constexpr int outputs_per_thread(int mode) { return mode == kABF ? 4 : 8; }
 
 // Warp groups per CTA that fit the shared-memory budget with `lut_n` table entries of kind `lut_kind` (0: none).
 int groups_that_fit(int mode, int radius, int lut_n, int lut_kind) {
-    for (int g = kMaxGroups; g >= 1; --g)
+    for (int g = max_groups(mode); g >= 1; --g)
         if (make_layout(mode, outputs_per_thread(mode), radius, lut_n, lut_kind, g).total <= kSmemBudget) return g;
     return 0;
 }
@@ -829,8 +929,20 @@ cudaError_t launch_tiled(const StencilArgs& a, int sm_count, cudaStream_t stream
     }
     const int n_groups = groups_that_fit(MODE, a.radius, a.lut_n * a.lut_rows, LK);
     if (n_groups < 1) return cudaErrorInvalidConfiguration;  // stencil_pick_lut never hands out such a table
-    const SmemLayout L = make_layout(MODE, P, a.radius, a.lut_n * a.lut_rows, LK, n_groups);
+    SmemLayout L = make_layout(MODE, P, a.radius, a.lut_n * a.lut_rows, LK, n_groups);
     auto kern = stencil_kernel<MODE, P, LK, PEER>;
+    if constexpr (MODE == kBF && !PEER && LK != kLutPremul) {
+        // TMA tile staging (opt-in): image rows 16-byte aligned and the staging rows fit next to the same warp groups
+        static const bool tma_on = [] {
+            const char* v = std::getenv("VIP_STENCIL_TMA");
+            return v && v[0] == '1';
+        }();
+        const SmemLayout Lt = make_layout(MODE, P, a.radius, a.lut_n * a.lut_rows, LK, n_groups, true);
+        if (tma_on && (reinterpret_cast<std::uintptr_t>(a.src) & 15u) == 0 && (a.width * 3) % 16 == 0 && Lt.total <= kSmemBudget) {
+            L = Lt;
+            kern = stencil_kernel<MODE, P, LK, false, true>;
+        }
+    }
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total);
     if (e != cudaSuccess) return e;
     const int tiles_x = (a.width + kWarps * P - 1) / (kWarps * P);
