@@ -225,6 +225,7 @@ def bind_to_gpu_numa_node(index):
         node = int(open(f"{base}/numa_node").read().strip())
         cpus = open(f"{base}/local_cpulist").read().strip()
         info["numa_node"], info["cpus"] = node, cpus
+        info["affinity_before"] = sorted(os.sched_getaffinity(0))
         if cpus:
             ids = set()
             for part in cpus.split(","):
@@ -808,6 +809,14 @@ def measure_job(ctx, name, steps, warmup, halo_mode, sampler=None, with_cpu=True
         ref_cuda["speedup_whole_job"] = ref_cuda["ms"] / ms_step
         out["ref_cuda"] = ref_cuda
     if with_cpu:
+        # the CPU baseline gets ALL host cores back (the process was pinned to the GPU's NUMA-local CPUs for its own
+        # pinned buffers; on a two-socket host that would halve the reference's threads)
+        before = ctx.placement.get("affinity_before")
+        if before:
+            try:
+                os.sched_setaffinity(0, before)
+            except OSError:
+                pass
         rows = sample_rows_for(filt, w, h, ksize, cpu_budget)
         mp, ckind, cores, what, _ = cpu_reference(filt, w, h, ksize, nitr, rows, ctx.args.cpu_threads, repeats=2, content=ctx.args.content)
         out["cpu_baseline"] = {"value": mp, "unit": "Mpixel/s", "cores": cores, "kind": ckind, "sample": what}
@@ -873,7 +882,7 @@ def main():
                "data": "lenna.png" if args.workload == "bf_lenna" else "synthetic"}
         out.update(main_out)
         out["clocks"] = clocks
-        out["host_placement"] = ctx.placement
+        out["host_placement"] = {k: v for k, v in ctx.placement.items() if k != "affinity_before"}
         if per:
             out["per_workload"] = per
         print(json.dumps(out), flush=True)
