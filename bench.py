@@ -294,15 +294,17 @@ def timed_steps(ctx, step, steps, warmup, sampler=None):
     ctx.barrier()
     m0 = sampler.mark() if sampler else 0
     n0 = vip.launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]   # one event per step boundary
+    evs[0].record()
     for i in range(steps):
         step(warmup + i)
-    ev1.record()
+        evs[i + 1].record()
     ctx.barrier()
     m1 = sampler.mark() if sampler else 0
     launches = vip.launch_count() - n0
-    return ctx.max_over_ranks(ev0.elapsed_time(ev1)) / steps, launches, (m0, m1)
+    per = [evs[i].elapsed_time(evs[i + 1]) for i in range(steps)]
+    stats = {"ms_median": ctx.max_over_ranks(float(np.median(per))), "ms_best": ctx.max_over_ranks(float(np.min(per)))}
+    return ctx.max_over_ranks(evs[0].elapsed_time(evs[steps])) / steps, launches, (m0, m1), stats
 
 
 class LinkTimeout(RuntimeError):
@@ -712,7 +714,7 @@ def measure_job(ctx, name, steps, warmup, halo_mode, sampler=None, with_cpu=True
     torch = ctx.torch
     job = Job(ctx, name, halo_mode)
     filt, w, h, ksize, nitr = job.filt, job.w, job.h, job.ksize, job.nitr
-    ms_step, launches, marks = timed_steps(ctx, job.step, steps, warmup, sampler)
+    ms_step, launches, marks, step_stats = timed_steps(ctx, job.step, steps, warmup, sampler)
     pixels_step = w * h if job.strong else w * h * ctx.world
     value = pixels_step / (ms_step * 1e-3) / 1e6
     e2e_steps = max(8, min(steps, 40))
@@ -838,6 +840,8 @@ def measure_job(ctx, name, steps, warmup, halo_mode, sampler=None, with_cpu=True
                                  "what": "the same pinned uploads + downloads on the same streams with no kernels, all ranks at once"},
                 "frac_of_copy_ceiling": ceil_s / e2e_s, "note": e2e_note},
         "gpu_launches": int(launches), "kernels_per_step": launches / max(steps, 1),
+        "step_ms": {"mean": ms_step, "median": step_stats["ms_median"], "best": step_stats["ms_best"],
+                    "what": "per-step CUDA events on the launching stream, max over ranks (SURVEY.md 8d asks for median and best)"},
         "dominant_kernel_launches_per_step": launches_of_kernel_per_step,
         "roofline": roof, "issue": issue, "_marks": (marks[0], marks[1], mark_end),
     }
