@@ -226,3 +226,28 @@ def test_strip_calls_random_row_ranges(vip, w, h, k, a, b, slack, kind, seed):
             vip.CudaBilateralTextureFilter(w, h, k, 1).iterate_strip(dev(img[s0:s1]), part, strip)
     torch.cuda.synchronize()
     assert torch.equal(part, whole[y0:y1])
+
+
+@settings(max_examples=30 * max(HUNT, 1), deadline=None, derandomize=not HUNT, suppress_health_check=SET["suppress_health_check"])
+@given(w=st.integers(4, 160), n=st.integers(2, 5), rows=st.integers(1, 60), k=st.sampled_from([3, 5, 9, 15, 21, 31, 35]),
+       kind=st.sampled_from(["bf", "abf"]), content=kinds, seed=st.integers(0, 10**6))
+def test_peer_halo_strips_random_cases(vip, w, n, rows, k, kind, content, seed):
+    """Strips whose halo rows are staged by the kernel from the NEIGHBOURS' buffers (struct vip_halo): every rank holds only
+    its own rows.  Any width, strip height >= radius (a halo never spans more than one neighbour), tiled and generic
+    kernels (k = 35), every content class: bit-exact against the oracle."""
+    r = k // 2
+    rows = max(rows, r)                      # a neighbour must be able to serve a whole halo
+    h = rows * n + (seed % 3)
+    img = make_image(w, h, content, seed)
+    want = O.o_abf(img, k) if kind == "abf" else O.o_bf(img, k)
+    f = vip.CudaAdaptiveBilateralFilter(w, h, k) if kind == "abf" else vip.CudaBilateralFilter(w, h, k)
+    plans = vip.plan_strips(h, n, r)
+    own = [dev(img[p.y0:p.y1]) for p in plans]
+    for i, p in enumerate(plans):
+        above = (own[i - 1], plans[i - 1].y0, plans[i - 1].y1 - plans[i - 1].y0) if i > 0 else None
+        below = (own[i + 1], plans[i + 1].y0, plans[i + 1].y1 - plans[i + 1].y0) if i + 1 < n else None
+        d = torch.zeros((p.y1 - p.y0, w, 3), dtype=torch.uint8, device="cuda")
+        st_ = vip.Strip(p.y0, p.y1 - p.y0, p.y0, p.y0, p.y1 - p.y0)
+        (f.execute_strip_peer if kind == "abf" else f.bilateral_filter_strip_peer)(own[i], vip.make_halo(above, below), d, st_)
+        torch.cuda.synchronize()
+        assert np.array_equal(d.cpu().numpy(), want[p.y0:p.y1]), (i, p)

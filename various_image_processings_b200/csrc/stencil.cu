@@ -257,15 +257,40 @@ __device__ __forceinline__ void run_taps(const typename Elem<MODE>::type* __rest
             const int j = n - 2 * p;  // tap of output 2p; output 2p+1 sees tap j-1
             const bool lo = j >= JLO && j < JHI, hi = j - 1 >= JLO && j - 1 < JHI;
             float wl = 0.f, wh = 0.f;
+            // VIP_PACK (A/B builds): 2 = everything packed (default), 1 = {s0,s1} packed but s2 / sk scalar, 0 = all scalar
+#ifndef VIP_PACK
+#define VIP_PACK 2
+#endif
+            auto acc01 = [&](unsigned long long& s01, const float wt) {
+                if constexpr (VIP_PACK >= 1) {
+                    fma2(s01, f01, pack2(wt, wt));
+                } else {
+                    float a0, a1;
+                    unpack2(s01, a0, a1);
+                    a0 = __fmaf_rn(f0, wt, a0);
+                    a1 = __fmaf_rn(f1, wt, a1);
+                    s01 = pack2(a0, a1);
+                }
+            };
             if (lo) {
                 wl = weight(q, A.c[2 * p], w[lo ? j - WOFF : 0]);
-                fma2(A.s01[2 * p], f01, pack2(wl, wl));
+                acc01(A.s01[2 * p], wl);
             }
             if (hi) {
                 wh = weight(q, A.c[2 * p + 1], w[hi ? j - 1 - WOFF : 0]);
-                fma2(A.s01[2 * p + 1], f01, pack2(wh, wh));
+                acc01(A.s01[2 * p + 1], wh);
             }
-            if (lo && hi) {
+            if (VIP_PACK < 2 && lo && hi) {
+                float x2, y2, xk, yk;
+                unpack2(A.s2[p], x2, y2);
+                unpack2(A.sk[p], xk, yk);
+                x2 = __fmaf_rn(f2, wl, x2);
+                y2 = __fmaf_rn(f2, wh, y2);
+                xk = __fadd_rn(xk, wl);
+                yk = __fadd_rn(yk, wh);
+                A.s2[p] = pack2(x2, y2);
+                A.sk[p] = pack2(xk, yk);
+            } else if (lo && hi) {
                 const unsigned long long ww = pack2(wl, wh);
                 fma2(A.s2[p], ww, pack2(f2, f2));
                 fma2(A.sk[p], ww, one2);
