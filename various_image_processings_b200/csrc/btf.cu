@@ -249,15 +249,22 @@ __global__ void __launch_bounds__(kThreads, 3) blur_rtv_kernel(const std::uint8_
     const int col = (warp & 1) * 32 + lane;
     const int r0 = (warp >> 1) * kRows;
     std::uint32_t sbr[kRows], sg[kRows], mn[kRows], mx[kRows];
-    float mm[kRows], msum[kRows];
+    float mm[kRows];
+    // raster-order magnitude sums of the outputs, two outputs (rows 2p, 2p+1) per packed fp32x2 register: while a tile row
+    // serves both, their chains advance with ONE FFMA2 per magnitude, acc = 1 * {m, m} + acc -- each half rounds exactly
+    // like the scalar add (fma(1, m, s) == s + m), half the issue slots of the K*K adds per output
+    unsigned long long msum2[kRows / 2];
 #pragma unroll
     for (int i = 0; i < kRows; ++i) {
         sbr[i] = sg[i] = 0;
         mn[i] = 0xffffu;
         mx[i] = 0;
         mm[i] = 0.f;
-        msum[i] = 0.f;
     }
+#pragma unroll
+    for (int p = 0; p < kRows / 2; ++p) msum2[p] = 0ull;
+    unsigned long long one2;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(one2) : "f"(1.f));
 #pragma unroll
     for (int R = 0; R < K + kRows - 1; ++R) {
         const uint4 h = hs[(r0 + R) * kTW + (col & ~7) + ((col + (col >> 3)) & 7)];
@@ -272,11 +279,33 @@ __global__ void __launch_bounds__(kThreads, 3) blur_rtv_kernel(const std::uint8_
                 mn[i] = min(mn[i], h.z & 0xffffu);
                 mx[i] = max(mx[i], h.z >> 16);
                 mm[i] = fmaxf(mm[i], __uint_as_float(h.w));
+            }
+        }
 #pragma unroll
-                for (int j = 0; j < K; ++j) msum[i] = __fadd_rn(msum[i], v[j]);
+        for (int p = 0; p < kRows / 2; ++p) {
+            const bool lo = R - 2 * p >= 0 && R - 2 * p < K, hi = R - 2 * p - 1 >= 0 && R - 2 * p - 1 < K;
+            if (lo && hi) {
+#pragma unroll
+                for (int j = 0; j < K; ++j) {
+                    unsigned long long vv;
+                    asm("mov.b64 %0, {%1, %1};" : "=l"(vv) : "f"(v[j]));
+                    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(msum2[p]) : "l"(one2), "l"(vv));
+                }
+            } else if (lo || hi) {
+                float a, b;
+                asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(msum2[p]));
+#pragma unroll
+                for (int j = 0; j < K; ++j) {
+                    if (lo) a = __fadd_rn(a, v[j]);
+                    else b = __fadd_rn(b, v[j]);
+                }
+                asm("mov.b64 %0, {%1, %2};" : "=l"(msum2[p]) : "f"(a), "f"(b));
             }
         }
     }
+    float msum[kRows];
+#pragma unroll
+    for (int p = 0; p < kRows / 2; ++p) asm("mov.b64 {%0, %1}, %2;" : "=f"(msum[2 * p]), "=f"(msum[2 * p + 1]) : "l"(msum2[p]));
 
     // E. epilogue (:88-103) and coalesced stores
     const int x = X0 + col;

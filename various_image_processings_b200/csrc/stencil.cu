@@ -324,6 +324,28 @@ __device__ __forceinline__ float abf_weight(const float d0, const float d1, cons
     return __fmul_rn(ks, lds_f32(addr));
 }
 
+// The same for the two outputs of a pair: the truncating add of 2^23 is ONE packed add.rz.f32x2 (each half rounds like
+// the scalar instruction), everything else as in abf_weight.  -DVIP_ABF_RZ2=0 builds the scalar form (A/B).
+#ifndef VIP_ABF_RZ2
+#define VIP_ABF_RZ2 1
+#endif
+template <int LK>
+__device__ __forceinline__ void abf_weight2(const float d0l, const float d1l, const float d2l, const float d0h,
+                                            const float d1h, const float d2h, const float ksl, const float ksh,
+                                            const std::uint32_t lut_addr, const float clamp_f, float& wl, float& wh) {
+    float distl = __fadd_rn(__fadd_rn(fabsf(d0l), fabsf(d1l)), fabsf(d2l));
+    float disth = __fadd_rn(__fadd_rn(fabsf(d0h), fabsf(d1h)), fabsf(d2h));
+    if constexpr (lut_clamped(LK)) {
+        distl = fminf(distl, clamp_f);
+        disth = fminf(disth, clamp_f);
+    }
+    unsigned long long t;
+    asm("add.rz.f32x2 %0, %1, %2;" : "=l"(t) : "l"(pack2(distl, disth)), "l"(pack2(8388608.f, 8388608.f)));
+    float tl, th;
+    unpack2(t, tl, th);
+    wl = __fmul_rn(ksl, lds_f32(lut_addr + (__float_as_uint(tl) << lut_shift(LK))));
+    wh = __fmul_rn(ksh, lds_f32(lut_addr + (__float_as_uint(th) << lut_shift(LK))));
+}
 // ABF run: outputs are handled in pairs (2p, 2p+1).  Neighbour n is tap j = n - 2p of the first and tap j - 1 of
 // the second output; when both are inside the run the differences and the four accumulations are packed fp32x2
 // operations (same IEEE roundings per half as the scalar ones), otherwise the one valid output goes scalar.
@@ -359,8 +381,13 @@ __device__ __forceinline__ void run_taps_abf(const std::uint32_t* __restrict__ t
                 unpack2(d0, d0l, d0h);
                 unpack2(d1, d1l, d1h);
                 unpack2(d2, d2l, d2h);
-                const float wl = abf_weight<LK>(d0l, d1l, d2l, w[j - WOFF], lut_addr, clamp_f);
-                const float wh = abf_weight<LK>(d0h, d1h, d2h, w[j - 1 - WOFF], lut_addr, clamp_f);
+                float wl, wh;
+                if constexpr (VIP_ABF_RZ2) {
+                    abf_weight2<LK>(d0l, d1l, d2l, d0h, d1h, d2h, w[j - WOFF], w[j - 1 - WOFF], lut_addr, clamp_f, wl, wh);
+                } else {
+                    wl = abf_weight<LK>(d0l, d1l, d2l, w[j - WOFF], lut_addr, clamp_f);
+                    wh = abf_weight<LK>(d0h, d1h, d2h, w[j - 1 - WOFF], lut_addr, clamp_f);
+                }
                 const unsigned long long ww = pack2(wl, wh);
                 fma2(A.s[0][p], ww, pack2(f0, f0));
                 fma2(A.s[1][p], ww, pack2(f1, f1));
