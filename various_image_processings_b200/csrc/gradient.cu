@@ -95,7 +95,10 @@ __device__ __forceinline__ int sq3(const std::uint32_t a, const std::uint32_t b)
 
 // A thread produces 4 columns x kFastRows rows: the kFastRows + 2 source rows it needs are read once as three aligned
 // words each and cut into pixels once; every row then serves as the upper, the centre and the lower neighbour.
-constexpr int kFastRows = 4;
+#ifndef VIP_GRAD_ROWS
+#define VIP_GRAD_ROWS 4
+#endif
+constexpr int kFastRows = VIP_GRAD_ROWS;   // -DVIP_GRAD_ROWS=8: A/B build
 __global__ void __launch_bounds__(256) gradient_u8c3_fast_kernel(const std::uint8_t* __restrict__ src,
                                                                  float* __restrict__ dst, const int W, const int H,
                                                                  const int src_y0, const int src_rows, const int dst_y0,
