@@ -208,6 +208,32 @@ VIP_API size_t vip_integral_table_elems(int width, int height, int radius);
 VIP_API int vip_integral_box_mean_u8c3(const uint32_t* d_table, float* d_mean, int width, int height, int radius,
                                        void* stream);
 
+/* vip_integral_u8c3_noalloc -- no counterpart in the reference; it exists for hosts that must not allocate.
+ *
+ * vip_integral_u8c3 above borrows its aggregate arrays (about a third of the table's size) from a CUDA memory pool on
+ * every call.  Some callers cannot afford that: a plug-in inside an application that has already given the whole GPU to
+ * its own allocator (the pool request then fails or steals memory the host did not budget for), a real-time or
+ * safety-reviewed loop where no driver allocation may happen after start-up, a process under an outer memory
+ * accountant.  This variant computes the identical table (bit for bit) and allocates NOTHING, neither device nor
+ * pinned memory, directly or through a library: the aggregates live in a fixed array of
+ * VIP_INTEGRAL_NOALLOC_SCRATCH_BYTES that is part of libvip_b200.so's device image.  You still pass the source
+ * image and the table (vip_integral_table_elems() uint32 elements), allocated however your host allows.
+ *
+ * Cost: that array occupies device memory on every GPU that loads the library's kernels, until the process exits,
+ * even if this function is never called.
+ * Limit: with tw = width+2r+1, th = height+2r+1 the call needs
+ *     (ceil(th/8) + ceil(th/32)) * tw * 3  +  2 * ceil(tw/256) * 3 * th      32-bit words;
+ * more than VIP_INTEGRAL_NOALLOC_SCRATCH_BYTES / 4 returns VIP_E_SIZE before anything is launched (3840x2160 fits
+ * up to r = 15 with room to spare; 7680x4320 does not fit -- use vip_integral_u8c3 there).
+ * First call on a device: looks up the array's address on the current device (cudaGetSymbolAddress, once per
+ * device, cached).  Make that first call outside any stream capture, with the device you will use current.
+ * Sharing: every call on a device uses the same array.  Calls are safe back to back on one stream (nothing needs
+ * clearing: each call writes every word before it reads it), but two calls that can overlap on the GPU -- different
+ * streams without an event between them, or two host threads -- race and produce garbage tables.  Serialise them. */
+#define VIP_INTEGRAL_NOALLOC_SCRATCH_BYTES (20u << 20)
+VIP_API int vip_integral_u8c3_noalloc(const uint8_t* d_src, uint32_t* d_table, int width, int height, int radius,
+                                      void* stream);
+
 /* Any source type / channel count of the reference template (BorderReplicatedIntegralImage<SrcType, Channels>,
  * instantiated by its tests for uint8_t / uint16_t / float x 1..3 channels,
  * test/border_replicated_integral_image.cpp:63-95).  src_type VIP_SRC_U8 / VIP_SRC_U16: uint32 table (modulo 2^32);

@@ -98,6 +98,7 @@ SIGNATURES = {
     "vip_convert_to_bgr_u8": (_i, [_vp, _i, _vp, _i, _i, _i, _vp]),
     "vip_scale_to_u8_f32": (_i, [_vp, _vp, _sz, _f, _vp]),
     "vip_integral_u8c3": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "vip_integral_u8c3_noalloc": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "vip_integral_get_u8c3": (_i, [_vp, _i, _i, _i, _vp, _i, _vp, _vp]),
     "vip_integral_table_elems": (_sz, [_i, _i, _i]),
     "vip_integral_build": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),

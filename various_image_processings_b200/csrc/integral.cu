@@ -27,6 +27,7 @@
 #include <mutex>
 #include <type_traits>
 
+#include "../../include/vip_c_api.h"
 #include "vip_internal.h"
 
 namespace vip {
@@ -489,3 +490,82 @@ cudaError_t launch_integral_box_mean(const std::uint32_t* table, float* mean, in
 }
 
 }  // namespace vip
+
+// ---------------------------------------------------------------------------------------------------------------
+// vip_integral_u8c3_noalloc: the integral image for callers that are not allowed to allocate device memory.
+//
+// vip_integral_u8c3 takes its aggregate arrays (band sums, band totals, row sums, row carries -- about 1/3 of the
+// table) from a stream-ordered memory pool.  That is a device allocation: it can fail when the process has handed all
+// of the GPU's memory to its own allocator, it may synchronise, and some hosts simply forbid it -- a plug-in running
+// inside an application that pre-reserves the whole device (a video pipeline with a fixed memory budget, an
+// inference server), a real-time loop that must not call the driver's allocator after start-up, or a process whose
+// memory is accounted by an outer framework that would not see ours.  This variant runs the same four kernels with the
+// aggregates in a fixed array that is part of the library image itself.
+//
+// The array costs kNoAllocWords * 4 bytes (20 MiB) on EVERY GPU on which the library's kernels get loaded, from the
+// first use until the process exits, whether or not this entry point is ever called.  Images whose aggregates do not
+// fit are refused (VIP_E_SIZE); a 3840x2160 frame fits up to radius 15, a 7680x4320 frame does not.
+constexpr size_t kNoAllocWords = size_t(5) << 20;
+static_assert(kNoAllocWords * sizeof(std::uint32_t) == VIP_INTEGRAL_NOALLOC_SCRATCH_BYTES, "header and array disagree");
+static __device__ __align__(256) std::uint32_t g_noalloc_scratch[kNoAllocWords];
+
+namespace {
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not somewhere a kernel could write; the real
+// device address differs per GPU and is looked up once per device with that device current.
+cudaError_t noalloc_scratch_ptr(std::uint32_t** out) {
+    static std::mutex mu;
+    static std::uint32_t* ptrs[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        ptrs[dev] = static_cast<std::uint32_t*>(p);
+    }
+    *out = ptrs[dev];
+    return cudaSuccess;
+}
+}  // namespace
+
+extern "C" VIP_API int vip_integral_u8c3_noalloc(const uint8_t* d_src, uint32_t* d_table, int width, int height,
+                                                  int radius, void* stream_) {
+    using namespace vip;
+    using A = std::uint32_t;
+    constexpr int C = 3;
+    if (!d_src || !d_table) return VIP_E_NULL;
+    if (width <= 0 || height <= 0 || radius < 0) return VIP_E_SIZE;
+    // 64-bit throughout: a caller probing the limit with absurd sizes must get VIP_E_SIZE, not a wrapped product
+    const long long tw = static_cast<long long>(width) + 2ll * radius + 1, th = static_cast<long long>(height) + 2ll * radius + 1;
+    const long long nsub = (th + kSubRows - 1) / kSubRows, nbands = (th + kBandRows - 1) / kBandRows;
+    const long long nchunks = (tw + kChunk - 1) / kChunk;
+    const long long row_elems = tw * C, rs_elems = nchunks * C * th;
+    if (tw > (1 << 24) || th > (1 << 24) || nsub > 65535) return VIP_E_SIZE;   // nsub is a grid y-dimension
+    const long long need = (nsub + nbands) * row_elems + 2 * rs_elems;
+    if (need > static_cast<long long>(kNoAllocWords)) return VIP_E_SIZE;
+    A* aux = nullptr;
+    const cudaError_t e = noalloc_scratch_ptr(&aux);   // first call on a device: one cudaGetSymbolAddress
+    if (e != cudaSuccess) return static_cast<int>(e);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    // Same carve-up and launch sequence as launch_integral_t.  Nothing has to be cleared between calls: every word
+    // a kernel reads (sub, tot, rowsum, carry) is written earlier in the same call by K1 / K2 / K2b for exactly the
+    // (row, column, chunk) ranges K3 reads, so whatever the previous call left behind is never looked at.
+    A* sub = aux;
+    A* tot = aux + nsub * row_elems;
+    A* rowsum = tot + nbands * row_elems;
+    A* carry = rowsum + rs_elems;
+    const dim3 g1(static_cast<unsigned>(nchunks), static_cast<unsigned>(nbands));
+    integral_bands_kernel<std::uint8_t, C><<<g1, kScanThreads, 0, stream>>>(d_src, sub, tot, rowsum, width, height, radius);
+    integral_band_scan_kernel<A><<<(static_cast<int>(row_elems) + 31) / 32, kScanThreads, 0, stream>>>(
+        tot, static_cast<int>(row_elems), static_cast<int>(nbands));
+    if (nchunks > 1)
+        integral_row_carry_kernel<A><<<dim3(static_cast<unsigned>(nchunks - 1), C), kCarryThreads, 0, stream>>>(
+            rowsum, carry, static_cast<int>(th), C);
+    integral_scan_kernel<std::uint8_t, C><<<dim3(static_cast<unsigned>(nchunks), static_cast<unsigned>(nsub)), kScanThreads, 0,
+                                            stream>>>(d_src, sub, tot, carry, d_table, width, height, radius);
+    count_launch(nchunks > 1 ? 4 : 3);
+    return static_cast<int>(cudaGetLastError());
+}
