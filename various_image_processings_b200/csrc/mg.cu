@@ -43,6 +43,17 @@ namespace {
 
 inline int cu(cudaError_t e) { return static_cast<int>(e); }
 
+// std::atomic<bool> that a std::vector element may be copied with (slots are only resized before any thread runs)
+struct SharedFlag {
+    std::atomic<bool> v{false};
+    SharedFlag() = default;
+    SharedFlag(const SharedFlag& o) : v(o.v.load(std::memory_order_relaxed)) {}
+    SharedFlag& operator=(const SharedFlag& o) {
+        v.store(o.v.load(std::memory_order_relaxed), std::memory_order_relaxed);
+        return *this;
+    }
+};
+
 struct Slot {
     int device = 0;
     int y0 = 0, rows = 0;      // owned rows
@@ -51,7 +62,7 @@ struct Slot {
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     std::vector<cudaEvent_t> ev_iter;  // BTF: iterate `it` is complete on this slot
     cudaEvent_t ev_pulled = nullptr;   // BTF exchange: this slot's last halo pull of a run is complete
-    bool pulled_valid = false;         // ev_pulled has been recorded by the previous run
+    SharedFlag pulled_valid;           // ev_pulled has been recorded by the previous run (written by this slot's worker, read by the neighbours')
     int peer_up = -1, peer_dn = -1;    // transport to the neighbouring slots: 1 P2P enabled, 0 staged through the host, -1 same device / none
     uint8_t* src = nullptr;            // rows [sy0, sy0+srows)
     uint8_t* buf[2] = {nullptr, nullptr};  // BF/ABF: buf[0] = dst (owned rows only); BTF: ping/pong over [sy0, ..)
@@ -84,6 +95,7 @@ struct vip_mg {
     std::vector<Slot> slots;
     std::vector<std::unique_ptr<Worker>> workers;          // one enqueueing thread per slot
     std::unique_ptr<std::atomic<int>[]> iter_recorded;     // BTF: iterations whose "done" event slot i has recorded
+    int unreported_rc = VIP_OK;  // first enqueue error of a run that was followed by another run before anybody asked
 };
 
 namespace {
@@ -176,7 +188,7 @@ int enqueue_slot(vip_mg* m, int i) {
         // recorded while run N was being enqueued, which vip_mg_run_async has waited for.
         if (!m->btf_deep) {
             for (int j = i - 1; j <= i + 1; j += 2) {
-                if (j < 0 || j >= m->n || !m->slots[j].pulled_valid) continue;
+                if (j < 0 || j >= m->n || !m->slots[j].pulled_valid.v.load(std::memory_order_acquire)) continue;
                 if ((e = cudaStreamWaitEvent(s.stream, m->slots[j].ev_pulled, 0)) != cudaSuccess) return cu(e);
             }
         }
@@ -221,7 +233,7 @@ int enqueue_slot(vip_mg* m, int i) {
         if (pulled) {
             if ((e = cudaEventRecord(s.ev_pulled, s.stream)) != cudaSuccess) return cu(e);
         }
-        s.pulled_valid = pulled;
+        s.pulled_valid.v.store(pulled, std::memory_order_release);
     }
     if ((e = cudaEventRecord(s.ev_stop, s.stream)) != cudaSuccess) return cu(e);
     return VIP_OK;
@@ -256,6 +268,21 @@ int wait_workers(vip_mg* m) {
         wp->cv.wait(lock, [&] { return wp->cmd_gen == wp->done_gen; });
         if (rc == VIP_OK) rc = wp->rc;
     }
+    return rc;
+}
+
+// wait_workers + hand out, exactly once, the first error since the last report: a run whose enqueueing failed and that
+// was followed by another vip_mg_run_async (no wait / gather in between) is reported by the next wait / gather.
+int take_run_status(vip_mg* m) {
+    int rc = VIP_OK;
+    for (auto& wp : m->workers) {
+        std::unique_lock<std::mutex> lock(wp->mu);
+        wp->cv.wait(lock, [&] { return wp->cmd_gen == wp->done_gen; });
+        if (rc == VIP_OK) rc = wp->rc;
+        wp->rc = VIP_OK;
+    }
+    if (m->unreported_rc != VIP_OK) rc = m->unreported_rc;   // the older error first
+    m->unreported_rc = VIP_OK;
     return rc;
 }
 
@@ -431,13 +458,13 @@ int vip_mg_scatter_device(vip_mg* m, const uint8_t* d_src_on_dev0) {
 
 int vip_mg_run_async(vip_mg* m) {
     if (!m) return VIP_E_NULL;
-    wait_workers(m);  // a previous run still being enqueued (its status was reported by its own wait / gather)
+    m->unreported_rc = take_run_status(m);  // a previous run still being enqueued; its error, if nobody has asked yet, stays pending
     for (int i = 0; i < m->n; i++) m->iter_recorded[i].store(0, std::memory_order_release);
     if (m->kind == VIP_MG_BTF) m->result_buf = m->nitr > 0 ? ((m->nitr - 1) & 1) : -1;
     for (auto& wp : m->workers) {
         {
             std::lock_guard<std::mutex> lock(wp->mu);
-            wp->rc = VIP_OK;   // a failed run does not poison the handle: every run reports its own status
+            wp->rc = VIP_OK;
             wp->cmd_gen++;
         }
         wp->cv.notify_all();
@@ -447,7 +474,7 @@ int vip_mg_run_async(vip_mg* m) {
 
 int vip_mg_wait(vip_mg* m) {
     if (!m) return VIP_E_NULL;
-    const int rc = wait_workers(m);
+    const int rc = take_run_status(m);
     if (rc != VIP_OK) return rc;
     DeviceGuard guard;
     for (Slot& s : m->slots) {
@@ -466,7 +493,7 @@ int vip_mg_run(vip_mg* m) {
 
 int vip_mg_gather_host(vip_mg* m, uint8_t* h_dst) {
     if (!m || !h_dst) return VIP_E_NULL;
-    const int wrc = wait_workers(m);
+    const int wrc = take_run_status(m);
     if (wrc != VIP_OK) return wrc;
     DeviceGuard guard;
     const size_t row_bytes = static_cast<size_t>(m->width) * 3;
@@ -538,26 +565,27 @@ static int batch_run_slot(vip_mg* m, int i, int set, const uint8_t* h_src, uint8
     cudaError_t e;
     int rc = batch_setup_slot(m, s, set);
     if (rc != VIP_OK) return rc;
+    // On an error the loop stops, but copies into the caller's h_dst that are already enqueued must have landed before
+    // this returns (the caller may free or reuse that memory): both lanes are synchronised on every path.
     int lane = 0;
-    for (int f = i; f < n_frames; f += m->n, lane ^= 1) {
+    for (int f = i; f < n_frames && rc == VIP_OK; f += m->n, lane ^= 1) {
         cudaStream_t st = s.bstream[lane];
-        if ((e = cudaMemcpyAsync(s.bsrc[lane], h_src + frame_bytes * f, frame_bytes, cudaMemcpyHostToDevice, st)) != cudaSuccess)
-            return cu(e);
-        if (set & VIP_MG_SET_BF)
-            if ((rc = vip_bf_run(s.bf, s.bsrc[lane], s.bdst[lane][0], st)) != VIP_OK) return rc;
-        if (set & VIP_MG_SET_ABF)
-            if ((rc = vip_abf_run(s.abf, s.bsrc[lane], s.bdst[lane][1], st)) != VIP_OK) return rc;
-        if (set & VIP_MG_SET_BTF)
-            if ((rc = vip_btf_run(s.bbtf[lane], s.bsrc[lane], s.bdst[lane][2], st)) != VIP_OK) return rc;
-        for (int j = 0; j < 3; j++)
+        if ((e = cudaMemcpyAsync(s.bsrc[lane], h_src + frame_bytes * f, frame_bytes, cudaMemcpyHostToDevice, st)) != cudaSuccess) {
+            rc = cu(e);
+            break;
+        }
+        if (rc == VIP_OK && (set & VIP_MG_SET_BF)) rc = vip_bf_run(s.bf, s.bsrc[lane], s.bdst[lane][0], st);
+        if (rc == VIP_OK && (set & VIP_MG_SET_ABF)) rc = vip_abf_run(s.abf, s.bsrc[lane], s.bdst[lane][1], st);
+        if (rc == VIP_OK && (set & VIP_MG_SET_BTF)) rc = vip_btf_run(s.bbtf[lane], s.bsrc[lane], s.bdst[lane][2], st);
+        for (int j = 0; j < 3 && rc == VIP_OK; j++)
             if (set >> j & 1)
                 if ((e = cudaMemcpyAsync(h_dst[j] + frame_bytes * f, s.bdst[lane][j], frame_bytes, cudaMemcpyDeviceToHost, st)) !=
                     cudaSuccess)
-                    return cu(e);
+                    rc = cu(e);
     }
     for (int l = 0; l < 2; l++)
-        if ((e = cudaStreamSynchronize(s.bstream[l])) != cudaSuccess) return cu(e);
-    return VIP_OK;
+        if (s.bstream[l] && (e = cudaStreamSynchronize(s.bstream[l])) != cudaSuccess && rc == VIP_OK) rc = cu(e);
+    return rc;
 }
 
 int vip_mg_run_batch_set_host(vip_mg* m, int filter_set, const uint8_t* h_src, uint8_t* const* h_dst, int n_frames) {
