@@ -374,7 +374,17 @@ VIP_API int vip_link_signal_ready(vip_link* l, int slot, unsigned step, void* st
 VIP_API int vip_link_wait_ready(vip_link* l, int slot, unsigned step, void* stream);
 VIP_API int vip_link_signal_consumed(vip_link* l, int slot, unsigned step, void* stream);
 VIP_API int vip_link_wait_consumed(vip_link* l, int slot, unsigned step, void* stream);
+/* vip_link_status: VIP_OK, or VIP_E_DEVICE once any wait of this link has timed out (synchronises the device).
+ * A timed-out wait does NOT stop the stream: the filter and the download enqueued behind it still run, on halo rows
+ * that are stale or missing.  So a frame produced through a link is only good if vip_link_status() is VIP_OK AFTER the
+ * frame's work has completed -- check it before the frame is consumed (per frame, or per batch of frames that is
+ * dropped as a whole).  The error stays latched until vip_link_reset().
+ * Same-device links (vip_link_connect_local on one GPU, or two processes sharing a GPU): the waits are spin kernels and
+ * need the signalling kernel of the other stream / process to run concurrently, which CUDA does not promise; that set-up
+ * is for functional tests, and the time-out is what bounds it.
+ * vip_link_reset: clears the latch (after synchronising the device); step counters are kept. */
 VIP_API int vip_link_status(vip_link* l);
+VIP_API int vip_link_reset(vip_link* l);
 
 #ifdef __cplusplus
 }

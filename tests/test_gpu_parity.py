@@ -579,7 +579,17 @@ def test_device_image_roundtrip(vip):
 
 
 # ------------------------------------------------------------------ the reference's own CUDA kernels, run on this GPU
-needs_ref_cuda = pytest.mark.skipif(not O.have_ref_cuda(), reason="oracle/_ref/libvip_ref_cuda.so not built")
+REF_MISSING = ("oracle/_ref/%s is missing on a GPU box: the exactness checks against the reference's own build would "
+               "silently not run.  It is built here by `make -C oracle ref` (needs /root/reference) and travels with the snapshot.")
+
+
+@pytest.fixture
+def _ref_cuda_required(vip):          # `vip` first: without a CUDA device the test is skipped, with one the library is REQUIRED
+    if not O.have_ref_cuda():
+        pytest.fail(REF_MISSING % "libvip_ref_cuda.so")
+
+
+needs_ref_cuda = pytest.mark.usefixtures("_ref_cuda_required")
 
 
 @needs_ref_cuda
@@ -774,6 +784,16 @@ def test_link_wait_times_out_instead_of_hanging(vip):
     torch.cuda.synchronize()
     with pytest.raises(vip.VipError):
         a.status()
+    with pytest.raises(vip.VipError):
+        a.status()                # latched: asking does not clear it
+    a.reset()
+    a.status()
+    # the link works again: a signalled step is seen
+    b.connect_local(a, None)
+    b.signal_ready(0, 1)
+    a.wait_ready(0, 1)
+    torch.cuda.synchronize()
+    a.status()
 
 
 @pytest.mark.parametrize("workload,halo", [("bf_4k_r5", "fused"), ("bf_4k_r5", "copy"), ("btf_1080p", "copy"), ("abf_1080p", "fused")])
@@ -817,9 +837,7 @@ def test_config_full_frame_equals_reference_cuda(vip, cfg, kind, w, h, k, nitr, 
     """The WHOLE frame of every BASELINE config, bit for bit against the reference's own CUDA kernels run on the same GPU
     (oracle/_ref/libvip_ref_cuda.so = src/*_impl.cu compiled unmodified; 3 - 25 ms each)."""
     if not O.have_ref_cuda():
-        pytest.skip("oracle/_ref/libvip_ref_cuda.so not built")
-    if content == "nat" and cfg == "C4":
-        pytest.skip("8K: S-rand only (time)")
+        pytest.fail(REF_MISSING % "libvip_ref_cuda.so")
     R = O.ref_cuda()
     if content == "rand":
         img = np.random.RandomState(42).randint(0, 256, size=(h, w, 3), dtype=np.uint8)
@@ -852,7 +870,7 @@ def test_btf_stage_fixtures_at_4k(vip):
     """The reference's stage tests (test/bilateral_texture_filter.cu:138-283: random magnitude / rtv / blurred inputs)
     at 3840 x 2160 against its own stage kernels: blurred + rtv and the guide bit for bit."""
     if not O.have_ref_cuda():
-        pytest.skip("oracle/_ref/libvip_ref_cuda.so not built")
+        pytest.fail(REF_MISSING % "libvip_ref_cuda.so")
     R = O.ref_cuda()
     w, h, k = 3840, 2160, 9
     n = w * h
@@ -891,7 +909,7 @@ BTF_O1_BOUNDS = {"rand": (0.0052, 0.0034), "nat": (1.5e-4, 4e-6), "smooth": (2e-
 @pytest.mark.parametrize("content", ["rand", "nat", "smooth"])
 def test_btf_vs_reference_cpu_report(vip, content):
     if not O.have_ref_cpu():
-        pytest.skip("oracle/_ref/libvip_ref_cpu.so not built")
+        pytest.fail(REF_MISSING % "libvip_ref_cpu.so")
     import sys
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
     import btf_o1_report as rep
@@ -992,3 +1010,42 @@ print("tma ok")
     env = dict(os.environ, VIP_STENCIL_TMA="1")
     p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env)
     assert p.returncode == 0 and "tma ok" in p.stdout, p.stderr[-2000:]
+
+
+def test_premultiplied_table_is_identical(vip):
+    """VIP_STENCIL_PREMUL=1 (read once per process, hence a subprocess): short colour tables are kept as one premultiplied
+    row RN(ks * lut[i]) per distinct spatial weight, the tap's multiply disappears (stencil.cu kLutPremul, capi.cu
+    init_tables).  The plan query must report lut_rows > 1 for the texture filter's joint bilateral step (k = 17,
+    sigma_color sqrt 3) and for a bilateral filter with a small sigma_color -- and the bytes out must not change."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = r'''
+import sys, ctypes as C, numpy as np, torch
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+import _oracle as O, various_image_processings_b200 as vip
+L = vip.capi.lib()
+def rows(mode, k, ss, sc):
+    plan = vip.capi.StencilPlan()
+    assert L.vip_stencil_plan_query(mode, k, ss, sc, C.byref(plan)) == 0
+    return plan.lut_rows
+sc3 = 3.0 ** 0.5
+assert rows(1, 17, 8.0, sc3) > 1, "JBF k=17 sigma_color sqrt(3) did not take the premultiplied table"
+assert rows(0, 9, 10.0, 2.0) > 1, "BF k=9 sigma_color 2 did not take the premultiplied table"
+assert rows(2, 9, 10.0, 2.0) == 1       # never for the adaptive filter
+for (w, h, k, ss, sc) in ((320, 96, 17, 8.0, sc3), (257, 70, 9, 4.0, sc3), (512, 64, 5, 10.0, 2.0), (200, 130, 9, 10.0, 2.0)):
+    img = O.rand_image(w, h, seed=w + k); guide = O.rand_image(w, h, seed=7 * w + k)
+    # a narrow-range image too: with sigma_color ~ 2 random bytes give all-zero weights off the centre
+    flat = (128 + (img %% 5)).astype(np.uint8); gflat = (128 + (guide %% 4)).astype(np.uint8)
+    for a, g in ((img, guide), (flat, gflat)):
+        d_a, d_g = torch.from_numpy(a).cuda(), torch.from_numpy(g).cuda(); d_dst = torch.empty_like(d_a)
+        F = vip.CudaBilateralFilter(w, h, k, ss, sc)
+        F.bilateral_filter(d_a, d_dst)
+        assert np.array_equal(d_dst.cpu().numpy(), O.o_bf(a, k, ss, sc)), ("bf", w, h, k)
+        F.joint_bilateral_filter(d_a, d_g, d_dst)
+        assert np.array_equal(d_dst.cpu().numpy(), O.o_jbf(a, g, k, ss, sc)), ("jbf", w, h, k)
+print("premul ok")
+''' % (root, os.path.join(root, "tests"))
+    env = dict(os.environ, VIP_STENCIL_PREMUL="1")
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env)
+    assert p.returncode == 0 and "premul ok" in p.stdout, (p.stdout[-500:], p.stderr[-2000:])

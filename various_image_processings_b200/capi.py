@@ -144,6 +144,7 @@ SIGNATURES = {
     "vip_link_signal_consumed": (_i, [_vp, _i, C.c_uint, _vp]),
     "vip_link_wait_consumed": (_i, [_vp, _i, C.c_uint, _vp]),
     "vip_link_status": (_i, [_vp]),
+    "vip_link_reset": (_i, [_vp]),
 }
 
 _lib = None

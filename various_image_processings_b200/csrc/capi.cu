@@ -153,6 +153,8 @@ int init_tables(StencilTables& T, int width, int height, int ksize, float ss, fl
             int n = 0, kind = 0;
             vip::stencil_pick_lut(static_cast<vip::StencilMode>(mode), r, table_len, T.last_nz, T.n_ks, &n, &kind);
             if (kind == vip::kStencilLutPremul) {
+                // BF and JBF share ONE premultiplied table: both modes must have picked the same row length
+                if (want_pm && T.pm_n != n) return VIP_E_UNSUPPORTED;
                 want_pm = true;
                 T.pm_n = n;
             }

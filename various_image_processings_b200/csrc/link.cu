@@ -253,4 +253,16 @@ int vip_link_status(vip_link* l) {
     return err ? VIP_E_DEVICE : VIP_OK;
 }
 
+/* Clears the latched time-out so that the link can be used again after the cause has been dealt with (neighbour
+ * restarted, steps re-agreed).  Synchronises the device first: no wait of this rank may still be spinning.  The step
+ * counters are NOT touched -- they are monotonic and shared with the neighbours. */
+int vip_link_reset(vip_link* l) {
+    if (!l) return VIP_E_NULL;
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) return cu(e);
+    const std::uint32_t zero = 0;
+    e = cudaMemcpy(l->flags + l->n_slots * kFlagsPerSlot, &zero, sizeof(zero), cudaMemcpyHostToDevice);
+    return cu(e);
+}
+
 }  // extern "C"

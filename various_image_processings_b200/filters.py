@@ -501,4 +501,9 @@ class StripLink:
         check(lib().vip_link_wait_consumed(self._h, slot, step, _stream(stream)), "vip_link_wait_consumed")
 
     def status(self):
+        """Raises VipError once any wait of this link has timed out; check it before a frame is consumed."""
         check(lib().vip_link_status(self._h), "vip_link_status")
+
+    def reset(self):
+        """Clears the latched time-out (the step counters stay)."""
+        check(lib().vip_link_reset(self._h), "vip_link_reset")
