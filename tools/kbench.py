@@ -111,7 +111,8 @@ def main():
         if R:
             ref_ms = timed(rr, n=2, warm=1)
             same = "EXACT" if torch.equal(d_dst, d_ref) else "DIFF(%d px)" % int((d_dst != d_ref).any(-1).sum().item())
-        print(f"{spec:22s} {ms:8.3f} ms  {w * h / ms / 1e3:9.0f} Mpix/s  {w * h * t_per_px / ms / 1e6:8.1f} Gtap/s   ref-cuda {ref_ms:9.3f} ms  x{ref_ms / ms:5.1f}  {same}", flush=True)
+        alg_bytes = w * h * (9 if kind == "jbf" else 6)     # u8 BGR in (+ guide) and out: the HBM floor
+        print(f"{spec:22s} {ms:8.3f} ms  {w * h / ms / 1e3:9.0f} Mpix/s  {w * h * t_per_px / ms / 1e6:8.1f} Gtap/s  {alg_bytes / ms / 1e6:7.1f} GB/s alg   ref-cuda {ref_ms:9.3f} ms  x{ref_ms / ms:5.1f}  {same}", flush=True)
 
 
 if __name__ == "__main__":
