@@ -172,17 +172,19 @@ def cpu_reference(filt, w, h, ksize, nitr, sample_rows, threads, repeats=1, cont
     return mpix, kind, cores, what, best
 
 
-def sample_rows_for(filt, w, h, ksize, budget_taps=1e9):
+def sample_rows_for(filt, w, h, ksize, budget_taps=1e9, min_rows=0):
+    """rows of the full-width crop the CPU legs filter; min_rows = 256 for the headline (a crop shorter than
+    that is mostly border rows of a radius-15 window), never more than the frame has"""
     taps = ksize * ksize * {"bf": 1, "abf": 2, "btf": 4, "all": 7}[filt]
     rows = int(budget_taps / (taps * w))
-    return max(4 * ksize, min(h, rows - rows % 8))
+    return min(h, max(4 * ksize, min_rows, rows - rows % 8))
 
 
 def run_reference_arm(args, wl):
     filt, w, h, ksize, nitr, desc = wl
     if int(os.environ.get("RANK", "0")) != 0:
         return
-    rows = sample_rows_for(filt, w, h, ksize)
+    rows = sample_rows_for(filt, w, h, ksize, min_rows=256)
     # calibrate once so that warmup + steps stay within ~2 minutes whatever the host is
     _, _, _, _, t_cal = cpu_reference(filt, w, h, ksize, nitr, rows, args.cpu_threads, content=args.content)
     budget_s = 120.0 / max(1, args.warmup + args.steps)
@@ -736,6 +738,84 @@ class Job:
         return res, ref_cuda
 
 
+def _events_ms(torch, fn, n, warm=3):
+    for i in range(warm):
+        fn(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(n):
+        fn(warm + i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n
+
+
+def time_btf_stages(vip, torch, job, srcs, jbf_ms):
+    """The kernels of the hot path that are not the dominant one, each timed alone with CUDA events on frames of the BTF
+    workload: one whole texture-filter iteration (3 launches), the guide kernel, the gradient and the integral image.
+    The fused gradient + blur/mRTV kernel has no entry point of its own: its time is iteration - guide - joint bilateral
+    (derived, and said so in the line)."""
+    w, h, k = job.w, job.h, job.ksize
+    n = 30
+    B = vip.CudaBilateralTextureFilter(w, h, k, 1)
+    outs = [torch.empty_like(srcs[0]) for _ in range(2)]
+    st = vip.Strip(0, h, 0, 0, h)
+    it_ms = _events_ms(torch, lambda i: B.iterate_strip(srcs[i % len(srcs)], outs[i & 1], st), n)
+    blurred = torch.rand((h, w, 3), dtype=torch.float32, device="cuda") * 255.0
+    rtv = torch.rand((h, w), dtype=torch.float32, device="cuda")
+    guide = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+    g_ms = _events_ms(torch, lambda i: B.compute_guide(blurred, rtv, guide), n)
+    mags = [torch.empty((h, w), dtype=torch.float32, device="cuda") for _ in range(4)]
+    grad_ms = _events_ms(torch, lambda i: vip.cuda_gradient(srcs[i % len(srcs)], mags[i % 4], w, h, 3), n)
+    r = 7
+    ii = vip.CudaIntegralImage(w, h, r)
+    int_ms = _events_ms(torch, lambda i: ii.build(srcs[i % len(srcs)]), n)
+    return {"iteration_ms": it_ms, "guide_ms": g_ms, "jbf_ms": jbf_ms, "gradient_ms": grad_ms, "integral_ms": int_ms, "integral_radius": r}
+
+
+def other_rooflines(t, w, h, k, issue_peak, issue_src, hbm_peak):
+    """roofline objects of the non-dominant kernels (round-2 review, item 5).  HBM side: algorithmic bytes / time against
+    the measured copy bandwidth.  Issue side (the BTF stages are instruction-bound): pixels/s x I_min
+    against the same measured FFMA issue rate as the stencils, with I_min(K) = the instructions the ARITHMETIC DEFINITION
+    needs per output pixel when nothing is wasted:
+      blur/mRTV  K^2/2 (the raster-order magnitude sum cannot be reordered: one FADD per tap, two outputs per packed FADD2)
+                 + K^2/8 (their shared-memory operand, one load per 8 outputs) + 2 x 6 x (K-1) (three box sums, min, max of
+                 b+g+r and max magnitude, separable: K-1 ops per quantity and pass) + 2K (record loads of the two passes)
+                 + 17 (gradient magnitude of the tile incl. halo) + 30 (three exact divides, the fp64 mRTV divide, stores)
+      guide      2 x 3 x (K-1) (lexicographic (value, index) min: compare + two selects per step, two passes) + 2K (loads)
+                 + 16 (alpha: expf, reciprocal) + 6 (gather of Bq, Bp) + 18 (blend, round, clamp of 3 channels) + 2 (store)"""
+    px = float(w * h)
+    K = float(k)
+    imin_blur = K * K / 2 + K * K / 8 + 12 * (K - 1) + 2 * K + 17 + 30
+    imin_guide = 6 * (K - 1) + 2 * K + 16 + 6 + 18 + 2
+    blur_ms = t["iteration_ms"] - t["guide_ms"] - t["jbf_ms"]
+    r = t["integral_radius"]
+    cells = float((w + 2 * r + 1) * (h + 2 * r + 1))
+
+    def hbm(bytes_, ms):
+        a = bytes_ / (ms * 1e-3) / 1e9
+        return {"achieved": a, "peak": hbm_peak, "unit": "GB/s", "frac": a / hbm_peak, "algorithmic_bytes_per_launch": bytes_}
+
+    def issue(imin, ms):
+        a = px * imin / (ms * 1e-3)
+        return {"achieved": a, "peak": issue_peak, "unit": "thread-instr/s", "frac": a / issue_peak if issue_peak else None,
+                "i_min_per_pixel": imin, "peak_source": issue_src}
+    out = {
+        "btf_iteration_ms": t["iteration_ms"],
+        "blur_rtv_kernel": {"bound": "issue", "kernel_ms": blur_ms, "timing": "derived: one whole iteration - guide kernel - joint bilateral kernel (each timed alone with CUDA events)",
+                            **issue(imin_blur, blur_ms), "hbm": hbm(px * (3 + 12 + 4), blur_ms)},
+        "guide_kernel": {"bound": "issue", "kernel_ms": t["guide_ms"], "timing": "alone, CUDA events, 30 launches",
+                         **issue(imin_guide, t["guide_ms"]), "hbm": hbm(px * (12 + 4 + 3), t["guide_ms"])},
+        "gradient_u8_kernel": {"bound": "hbm", "kernel_ms": t["gradient_ms"], "timing": "alone, CUDA events, 30 launches, rotating frames",
+                               **hbm(px * 7, t["gradient_ms"])},
+        "integral_kernels": {"bound": "hbm", "kernel_ms": t["integral_ms"], "radius": r, "launches": 4,
+                             "timing": "alone (4 launches + pool allocation), CUDA events, 30 builds, rotating frames",
+                             **hbm(cells * 15, t["integral_ms"])},
+    }
+    return out
+
+
 def measure_job(ctx, name, steps, warmup, halo_mode, sampler=None, with_cpu=True, cpu_budget=1e9):
     """All figures of one workload; rank 0 gets the dict, the others None."""
     import various_image_processings_b200 as vip
@@ -783,6 +863,7 @@ def measure_job(ctx, name, steps, warmup, halo_mode, sampler=None, with_cpu=True
     # ---- the dominant kernel, timed alone where a step is several kernels (BTF: the joint bilateral, 2k-1 window,
     #      sigma_space k-1, sigma_color sqrt 3 -- src/bilateral_texture_filter_impl.cu:188), CUDA events, same frames
     local_rows = job.own
+    stage_times = None
     if filt in ("btf", "all"):
         kind = "jbf"
         radius = ksize - 1
@@ -812,6 +893,8 @@ def measure_job(ctx, name, steps, warmup, halo_mode, sampler=None, with_cpu=True
         kernel_ms = j0.elapsed_time(j1) / jn
         launches_of_kernel_per_step = nitr
         alg_bytes = w * local_rows * 9.0
+        if filt == "btf" and not job.strong and nitr > 0:
+            stage_times = time_btf_stages(vip, torch, job, srcs, kernel_ms)
     else:
         kind = filt
         radius = ksize // 2
@@ -862,6 +945,8 @@ def measure_job(ctx, name, steps, warmup, halo_mode, sampler=None, with_cpu=True
         roof["peak"], roof["peak_source"] = nominal, "nominal: SMs x 128 thread-instr/clk x max SM clock (probe not run)"
         roof["frac"] = roof["achieved"] / nominal
 
+    other = other_rooflines(stage_times, w, h, ksize, roof["peak"], roof.get("peak_source"), hbm_peak) if stage_times else None
+
     out = {
         "metric": f"{filt}_throughput", "value": value, "unit": "Mpixel/s", "ms_per_step": head_ms, "steps": steps, "warmup": warmup,
         # one frame's work is fixed and cut into N strips (strong) wherever the filter and the frame allow it -- at N = 1 the
@@ -894,6 +979,8 @@ def measure_job(ctx, name, steps, warmup, halo_mode, sampler=None, with_cpu=True
                           "what": "N independent strip kernels whose halo rows come from neighbours' STATIC pool frames: no neighbour ordering, no per-step coupling -- kernel cost of a strip only (this was `value` in rounds 1-2); roofline.kernel_ms is this leg and, in halo mode 'copy', includes the halo copy"}}
         out["gpu_launches"] = ordered["launches"]
         out["kernels_per_step"] = ordered["launches"] / max(steps, 1)
+    if other:
+        out["other_kernels"] = other
     if parity is not None:
         out["strip_parity"] = parity["verdict"]
         out["parity"] = parity
@@ -909,9 +996,19 @@ def measure_job(ctx, name, steps, warmup, halo_mode, sampler=None, with_cpu=True
                 os.sched_setaffinity(0, before)
             except OSError:
                 pass
-        rows = sample_rows_for(filt, w, h, ksize, cpu_budget)
-        mp, ckind, cores, what, _ = cpu_reference(filt, w, h, ksize, nitr, rows, ctx.args.cpu_threads, repeats=2, content=ctx.args.content)
+        headline = cpu_budget >= 1e9
+        rows = sample_rows_for(filt, w, h, ksize, cpu_budget, min_rows=256 if headline else 0)
+        mp, ckind, cores, what, t_all = cpu_reference(filt, w, h, ksize, nitr, rows, ctx.args.cpu_threads, repeats=2, content=ctx.args.content)
         out["cpu_baseline"] = {"value": mp, "unit": "Mpixel/s", "cores": cores, "kind": ckind, "sample": what}
+        if headline and cores > 1:
+            # the ONE-core row: same code, one thread, on a crop sized from the all-cores time so that it
+            # takes about 8 s whatever the host is
+            rows1 = int(rows * 8.0 / max(t_all * cores, 1e-3)) // 8 * 8
+            rows1 = min(rows, max(2 * ksize, rows1))
+            mp1, _, _, what1, _ = cpu_reference(filt, w, h, ksize, nitr, rows1, 1, repeats=1, content=ctx.args.content)
+            out["cpu_baseline"]["one_core"] = {"value": mp1, "unit": "Mpixel/s", "cores": 1, "sample": what1,
+                                               "all_cores_speedup": mp / mp1}
+            out["cpu_baseline"]["not_measured"] = "a -march=native build of the reference: oracle/_ref is compiled where /root/reference exists (not on the GPU box), for a generic x86-64 target"
     return out, job
 
 
